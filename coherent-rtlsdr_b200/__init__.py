@@ -1,0 +1,227 @@
+"""coherent-rtlsdr_b200 -- Python face of libcoherent_cuda.so (ctypes over the C ABI).
+
+The product is the shared library in ``lib/`` (sources in ``csrc/``, ABI in
+``include/coherent_cuda.h``).  This module only loads it and marshals numpy / raw pointers; it
+contains no arithmetic and has no CPU fallback: if the library is missing or no CUDA device is
+usable, construction raises.
+
+The directory name carries a hyphen (it mirrors the reference's repository name), so import it
+through ``cohpkg.load()`` at the repository root.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libcoherent_cuda.so")
+
+LAG_NONE, LAG_ALL = 0, 1
+
+# every symbol include/coherent_cuda.h declares
+ABI_SYMBOLS = [
+    "cohcuda_create", "cohcuda_destroy", "cohcuda_last_error", "cohcuda_register_host",
+    "cohcuda_unregister_host", "cohcuda_packet_layout", "cohcuda_submit_block",
+    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_launch_count",
+    "cohcuda_device_packets", "cohcuda_get_state", "cohcuda_set_state",
+    "cohcuda_cdsp_convtosigned", "cohcuda_cdsp_convtofloat", "cohcuda_cdsp_convto8bit",
+    "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
+    "cohcuda_cdsp_conjugatemul", "cohcuda_cdsp_indexofmax", "cohcuda_cdsp_rms",
+    "cohcuda_cdsp_fft",
+]
+
+
+class Config(C.Structure):
+    _fields_ = [("n_signal", C.c_uint32), ("blocksize", C.c_uint32), ("max_lag_slots", C.c_uint32),
+                ("alpha", C.c_float), ("noheader", C.c_int), ("apply_shift", C.c_int),
+                ("device", C.c_int), ("max_batch_blocks", C.c_uint32), ("stream", C.c_void_p)]
+
+
+class ChanState(C.Structure):
+    _fields_ = [("phasecorr", C.c_float * 2), ("phasecorrprev", C.c_float * 2),
+                ("lag", C.c_float), ("mag", C.c_float), ("held_lag", C.c_int32)]
+
+
+class Result(C.Structure):
+    _fields_ = [("lag", C.POINTER(C.c_float)), ("mag", C.POINTER(C.c_float)),
+                ("phasecorr", C.POINTER(C.c_float)), ("measured", C.POINTER(C.c_uint8)),
+                ("packet", C.POINTER(C.c_int8)), ("packet_len", C.c_size_t),
+                ("globalseqn", C.c_uint32)]
+
+
+class BatchArgs(C.Structure):
+    _fields_ = [("iq", C.c_void_p), ("iq_on_device", C.c_int), ("n_blocks", C.c_uint32),
+                ("lag_request", C.c_void_p), ("lag_mode", C.c_int), ("refnoise", C.c_void_p),
+                ("refnoise_enabled", C.c_int), ("input_is_signed", C.c_int),
+                ("readcnt", C.c_void_p), ("readcnt0", C.c_uint32), ("globalseqn0", C.c_uint32),
+                ("packets", C.c_void_p), ("packets_on_device", C.c_int), ("lag", C.c_void_p),
+                ("mag", C.c_void_p), ("phasecorr", C.c_void_p), ("cf32", C.c_void_p)]
+
+
+class CohCudaError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libcoherent_cuda.so and declare prototypes.  Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CohCudaError(f"{LIB_PATH} is missing: run `make` (or __graft_entry__.build()); "
+                           "there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, i, u32 = C.c_void_p, C.c_int, C.c_uint32
+    L.cohcuda_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.cohcuda_destroy.argtypes = [vp]; L.cohcuda_destroy.restype = None
+    L.cohcuda_last_error.argtypes = [vp]; L.cohcuda_last_error.restype = C.c_char_p
+    L.cohcuda_register_host.argtypes = [vp, vp, C.c_size_t]
+    L.cohcuda_unregister_host.argtypes = [vp, vp]
+    L.cohcuda_packet_layout.argtypes = [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+    L.cohcuda_submit_block.argtypes = [vp, C.POINTER(vp), vp, vp, i, i]
+    L.cohcuda_wait_block.argtypes = [vp, C.POINTER(Result)]
+    L.cohcuda_batch.argtypes = [vp, C.POINTER(BatchArgs)]
+    L.cohcuda_sync.argtypes = [vp]
+    L.cohcuda_launch_count.argtypes = [vp]; L.cohcuda_launch_count.restype = C.c_uint64
+    L.cohcuda_device_packets.argtypes = [vp]; L.cohcuda_device_packets.restype = vp
+    L.cohcuda_get_state.argtypes = [vp, vp, u32]
+    L.cohcuda_set_state.argtypes = [vp, vp, u32]
+    L.cohcuda_cdsp_convtosigned.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_convtofloat.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_convto8bit.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_scalarmul.argtypes = [vp, vp, vp, C.c_float, C.c_float, i]
+    L.cohcuda_cdsp_conj_dotproduct.argtypes = [vp, vp, vp, vp, i]
+    L.cohcuda_cdsp_magsquared.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_conjugatemul.argtypes = [vp, vp, vp, vp, i]
+    L.cohcuda_cdsp_indexofmax.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_rms.argtypes = [vp, vp, vp, i]
+    L.cohcuda_cdsp_fft.argtypes = [vp, vp, vp, i, i, i]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    return a.ctypes.data
+
+
+class CoherentCuda:
+    """One handle = one GPU rank's block sync + correction engine (mirrors ccoherent +
+    the DSP members of csdrdevice + cpacketize::write in the reference)."""
+
+    def __init__(self, n_signal, blocksize, alpha=0.5, noheader=False, apply_shift=False,
+                 max_lag_slots=0, device=0, max_batch_blocks=1, stream=None):
+        self.lib = load_library()
+        self.cfg = Config(n_signal, blocksize, max_lag_slots, alpha, int(noheader), int(apply_shift),
+                          device, max_batch_blocks, stream)
+        self.h = C.c_void_p()
+        rc = self.lib.cohcuda_create(C.byref(self.cfg), C.byref(self.h))
+        if rc != 0:
+            self.h = None
+            raise CohCudaError(f"cohcuda_create failed ({rc}): {self.lib.cohcuda_last_error(None).decode()}")
+        self.n_signal, self.nch, self.B, self.L = n_signal, n_signal + 1, blocksize, blocksize // 2
+        pl, pitch, lead = C.c_size_t(), C.c_size_t(), C.c_size_t()
+        self.lib.cohcuda_packet_layout(self.h, C.byref(pl), C.byref(pitch), C.byref(lead))
+        self.packet_len, self.dev_pitch, self.dev_lead = pl.value, pitch.value, lead.value
+        self.hdr_len = 0 if noheader else 16 + 4 * self.nch
+        self._keep = []
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise CohCudaError(f"{what} failed ({rc}): {self.lib.cohcuda_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cohcuda_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- batch ------------------------------------------------------------------------------
+    def batch_raw(self, **kw):
+        """Thin call: keyword names are cohcuda_batch_args fields; pointers as ints/ndarrays."""
+        a = BatchArgs()
+        for k, v in kw.items():
+            setattr(a, k, _ptr(v) if k in ("iq", "lag_request", "refnoise", "readcnt", "packets",
+                                            "lag", "mag", "phasecorr", "cf32") else v)
+        self._check(self.lib.cohcuda_batch(self.h, C.byref(a)), "cohcuda_batch")
+
+    def sync(self):
+        self._check(self.lib.cohcuda_sync(self.h), "cohcuda_sync")
+
+    def batch(self, iq, lag_mode=LAG_ALL, lag_request=None, refnoise=None, refnoise_enabled=True,
+              input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0):
+        """Host-array convenience: iq uint8 [n_blocks][C+1][B] -> dict of numpy outputs."""
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        nb = iq.shape[0]
+        assert iq.shape[1:] == (self.nch, self.B), iq.shape
+        out = {
+            "packets": np.zeros((nb, self.packet_len), dtype=np.int8),
+            "lag": np.zeros((nb, self.nch), dtype=np.float32),
+            "mag": np.zeros((nb, self.nch), dtype=np.float32),
+            "phase": np.zeros((nb, self.nch), dtype=np.complex64),
+        }
+        lr = None if lag_request is None else np.ascontiguousarray(lag_request, dtype=np.uint8)
+        rn = None if refnoise is None else np.ascontiguousarray(refnoise, dtype=np.uint8)
+        rc_ = None if readcnt is None else np.ascontiguousarray(readcnt, dtype=np.uint32)
+        self.batch_raw(iq=iq, iq_on_device=0, n_blocks=nb, lag_request=lr, lag_mode=int(lag_mode),
+                       refnoise=rn, refnoise_enabled=int(refnoise_enabled),
+                       input_is_signed=int(input_is_signed), readcnt=rc_, readcnt0=readcnt0,
+                       globalseqn0=globalseqn0, packets=out["packets"], packets_on_device=0,
+                       lag=out["lag"], mag=out["mag"], phasecorr=out["phase"])
+        self.sync()
+        return out
+
+    # ---- per-block streaming ------------------------------------------------------------------
+    def submit_block(self, chans, readcnt=None, lag_request=None, refnoise_enabled=True,
+                     input_is_signed=False):
+        arr = (C.c_void_p * self.nch)(*[c.ctypes.data for c in chans])
+        rc_ = None if readcnt is None else np.ascontiguousarray(readcnt, dtype=np.uint32)
+        lr = None if lag_request is None else np.ascontiguousarray(lag_request, dtype=np.uint8)
+        self._keep = [chans, rc_, lr, arr]
+        self._check(self.lib.cohcuda_submit_block(self.h, arr, _ptr(rc_), _ptr(lr),
+                                                  int(refnoise_enabled), int(input_is_signed)),
+                    "cohcuda_submit_block")
+
+    def wait_block(self):
+        r = Result()
+        self._check(self.lib.cohcuda_wait_block(self.h, C.byref(r)), "cohcuda_wait_block")
+        n = self.nch
+        return {
+            "lag": np.ctypeslib.as_array(r.lag, (n,)).copy(),
+            "mag": np.ctypeslib.as_array(r.mag, (n,)).copy(),
+            "phase": np.ctypeslib.as_array(r.phasecorr, (2 * n,)).copy().view(np.complex64),
+            "measured": np.ctypeslib.as_array(r.measured, (n,)).copy(),
+            "packet": np.ctypeslib.as_array(r.packet, (r.packet_len,)).copy(),
+            "globalseqn": r.globalseqn,
+        }
+
+    # ---- state ----------------------------------------------------------------------------------
+    def get_state(self):
+        st = (ChanState * self.nch)()
+        self._check(self.lib.cohcuda_get_state(self.h, st, self.nch), "cohcuda_get_state")
+        return st
+
+    def set_state(self, st):
+        self._check(self.lib.cohcuda_set_state(self.h, st, self.nch), "cohcuda_set_state")
+
+    def launch_count(self):
+        return int(self.lib.cohcuda_launch_count(self.h))
+
+    def register_host(self, arr):
+        self._check(self.lib.cohcuda_register_host(self.h, arr.ctypes.data, arr.nbytes), "cohcuda_register_host")
+
+    def unregister_host(self, arr):
+        self._check(self.lib.cohcuda_unregister_host(self.h, arr.ctypes.data), "cohcuda_unregister_host")

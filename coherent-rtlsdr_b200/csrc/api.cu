@@ -1,0 +1,274 @@
+// api.cu -- C ABI of libcoherent_cuda (include/coherent_cuda.h): handle, buffers, the batch
+// schedule (K1 ref spectrum -> K2 correlate -> K3 apply) and the per-block streaming calls.
+// Host-side only; kernels live in fft_kernels.cu / apply_kernel.cu / prims.cu.
+#include "coherent_cuda.h"
+#include "kernels.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace coh;
+
+static std::string g_create_error;
+
+struct cohcuda {
+    cohcuda_config cfg{};
+    uint32_t nch = 0, B = 0, L = 0;
+    size_t hdr = 0, plen = 0, pitch = 0, lead = 0;
+    int sm_count = 0, lookback = 48;
+    cudaStream_t stream = nullptr, s_in = nullptr, s_out = nullptr;
+    bool own_stream = false;
+    std::string err;
+    uint64_t launches = 0;
+
+    float2 *d_TN = nullptr;
+    ChanState *d_state[2] = { nullptr, nullptr };
+    int cur = 0;
+    uint32_t *d_ticket = nullptr; uint32_t ticket_total = 0, epoch = 0;
+
+    uint32_t cap = 0;                                   // capacity in blocks
+    uint8_t *d_iq = nullptr; int8_t *d_packets = nullptr;
+    float2 *d_refspec = nullptr; PeakRec *d_peaks = nullptr;
+    float *d_lag = nullptr, *d_mag = nullptr; float2 *d_phase = nullptr; uint8_t *d_meas = nullptr;
+    float2 *d_q = nullptr; uint32_t *d_flag = nullptr; int2 *d_partial = nullptr; uint32_t *d_pflag = nullptr;
+    int32_t *d_src = nullptr; uint32_t *d_items = nullptr, *d_reflist = nullptr, *d_slot = nullptr;
+    uint8_t *d_refnoise = nullptr; uint32_t *d_readcnt = nullptr;
+    const int8_t *last_packets = nullptr;
+
+    // pinned staging for the per-block streaming calls
+    uint8_t *h_flags = nullptr; uint32_t *h_readcnt = nullptr;
+    float *h_lag = nullptr, *h_mag = nullptr, *h_phase = nullptr; uint8_t *h_meas = nullptr;
+    int8_t *h_packet[2] = { nullptr, nullptr };
+    int pk = 0; bool pending = false; uint32_t seq = 0;
+    std::vector<cudaEvent_t> ev_in, ev_done;
+    cudaEvent_t ev_start = nullptr, ev_out = nullptr;
+    std::vector<void *> registered;
+};
+
+static constexpr uint32_t kCorrChunk = 148;             // blocks per K1/K2 launch: items = 148*C
+
+#define CK(call)                                                                        \
+    do {                                                                                \
+        cudaError_t e__ = (call);                                                       \
+        if (e__ != cudaSuccess) {                                                       \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e__);               \
+            return COHCUDA_ERR_CUDA;                                                    \
+        }                                                                               \
+    } while (0)
+
+template <typename T> static cudaError_t dalloc(T **p, size_t n) {
+    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, n * sizeof(T));
+    return e;
+}
+template <typename T> static void dfree(T *&p) { if (p) cudaFree(p); p = nullptr; }
+
+static void free_batch_buffers(cohcuda *h) {
+    dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_refspec); dfree(h->d_peaks);
+    dfree(h->d_lag); dfree(h->d_mag); dfree(h->d_phase); dfree(h->d_meas);
+    dfree(h->d_q); dfree(h->d_flag); dfree(h->d_partial); dfree(h->d_pflag);
+    dfree(h->d_src); dfree(h->d_items); dfree(h->d_reflist); dfree(h->d_slot);
+    dfree(h->d_refnoise); dfree(h->d_readcnt);
+    h->cap = 0;
+}
+
+static int ensure_capacity(cohcuda *h, uint32_t nb) {
+    if (nb <= h->cap) return COHCUDA_OK;
+    CK(cudaStreamSynchronize(h->stream));
+    free_batch_buffers(h);
+    const size_t n = (size_t)nb * h->nch, parts = apply_parts(h->B);
+    CK(dalloc(&h->d_iq, n * h->B));
+    CK(dalloc(&h->d_packets, (size_t)nb * h->pitch + 16));
+    if (correlate_supported(h->B))
+        CK(dalloc(&h->d_refspec, (size_t)kCorrChunk * 2 * h->L));
+    CK(dalloc(&h->d_peaks, n));
+    CK(dalloc(&h->d_lag, n)); CK(dalloc(&h->d_mag, n)); CK(dalloc(&h->d_phase, n)); CK(dalloc(&h->d_meas, n));
+    CK(dalloc(&h->d_q, n)); CK(dalloc(&h->d_flag, n));
+    CK(dalloc(&h->d_partial, n * parts)); CK(dalloc(&h->d_pflag, n * parts));
+    CK(dalloc(&h->d_src, n)); CK(dalloc(&h->d_items, n)); CK(dalloc(&h->d_reflist, (size_t)nb)); CK(dalloc(&h->d_slot, (size_t)nb));
+    CK(dalloc(&h->d_refnoise, (size_t)nb)); CK(dalloc(&h->d_readcnt, n));
+    h->cap = nb;
+    return COHCUDA_OK;
+}
+
+extern "C" const char *cohcuda_last_error(cohcuda_t *h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
+    if (!cfg || !out) { g_create_error = "null argument"; return COHCUDA_ERR_ARG; }
+    *out = nullptr;
+    const uint32_t B = cfg->blocksize;
+    if (B < 64 || (B & (B - 1)) || cfg->n_signal == 0 || cfg->n_signal > 65535) {
+        g_create_error = "blocksize must be a power of two >= 64 and n_signal in 1..65535";
+        return COHCUDA_ERR_ARG;
+    }
+    if (!(cfg->alpha > 0.0f && cfg->alpha <= 1.0f)) { g_create_error = "alpha must be in (0,1]"; return COHCUDA_ERR_ARG; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) {
+        g_create_error = std::string("no usable CUDA device (there is no CPU fallback): ") +
+                         (e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal out of range");
+        return COHCUDA_ERR_CUDA;
+    }
+    cohcuda *h = new (std::nothrow) cohcuda();
+    if (!h) { g_create_error = "out of host memory"; return COHCUDA_ERR_NOMEM; }
+    h->cfg = *cfg; h->B = B; h->L = B / 2; h->nch = cfg->n_signal + 1;
+    h->hdr = cfg->noheader ? 0 : 16 + 4 * (size_t)h->nch;
+    h->plen = h->hdr + (size_t)h->nch * B;
+    h->lead = (16 - h->hdr % 16) % 16;
+    h->pitch = (h->lead + h->plen + 15) / 16 * 16;
+    // look-back depth: truncated IIR tail weight (1-alpha)^depth <= 2^-48
+    if (cfg->alpha >= 1.0f) h->lookback = 1;
+    else {
+        double d = std::ceil(48.0 * std::log(2.0) / -std::log(1.0 - (double)cfg->alpha));
+        h->lookback = (int)std::fmin(std::fmax(d, 1.0), 2048.0);
+    }
+    auto fail = [&](const char *what, cudaError_t ce) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
+        cohcuda_destroy(h);
+        return COHCUDA_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, cfg->device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+    h->sm_count = prop.multiProcessorCount;
+    if (cfg->stream) h->stream = (cudaStream_t)cfg->stream;
+    else {
+        if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+        h->own_stream = true;
+    }
+    if ((e = cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    // twiddle table: exp(-2*pi*i*n/N), n < L, N = 2L, computed in double and rounded once
+    {
+        std::vector<float2> tn(h->L);
+        for (uint32_t n = 0; n < h->L; n++) {
+            double a = -2.0 * M_PI * (double)n / (double)(2 * h->L);
+            tn[n] = make_float2((float)std::cos(a), (float)std::sin(a));
+        }
+        if ((e = cudaMalloc((void **)&h->d_TN, sizeof(float2) * h->L)) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMemcpy(h->d_TN, tn.data(), sizeof(float2) * h->L, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+    }
+    for (int i = 0; i < 2; i++)
+        if ((e = dalloc(&h->d_state[i], (size_t)h->nch)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = dalloc(&h->d_ticket, (size_t)1)) != cudaSuccess) return fail("cudaMalloc", e);
+    {
+        std::vector<ChanState> st(h->nch);
+        for (auto &s : st) {            // csdrdevice.cc:36-40
+            s.phasecorr = make_float2(1.f, 0.f); s.phasecorrprev = make_float2(1.f, 0.f);
+            s.lag = 0.f; s.mag = 0.f; s.held_lag = 0; s.pad = 0;
+        }
+        for (int i = 0; i < 2; i++)
+            if ((e = cudaMemcpy(h->d_state[i], st.data(), sizeof(ChanState) * h->nch, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+    }
+    const size_t n1 = h->nch;
+    if ((e = cudaMallocHost((void **)&h->h_flags, n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void **)&h->h_readcnt, 4 * n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void **)&h->h_lag, 4 * n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void **)&h->h_mag, 4 * n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void **)&h->h_phase, 8 * n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    if ((e = cudaMallocHost((void **)&h->h_meas, n1)) != cudaSuccess) return fail("cudaMallocHost", e);
+    for (int i = 0; i < 2; i++)
+        if ((e = cudaMallocHost((void **)&h->h_packet[i], h->plen)) != cudaSuccess) return fail("cudaMallocHost", e);
+    int rc = ensure_capacity(h, cfg->max_batch_blocks ? cfg->max_batch_blocks : 1);
+    if (rc != COHCUDA_OK) { g_create_error = h->err; cohcuda_destroy(h); return rc; }
+    *out = h;
+    return COHCUDA_OK;
+}
+
+extern "C" void cohcuda_destroy(cohcuda_t *h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (void *p : h->registered) cudaHostUnregister(p);
+    free_batch_buffers(h);
+    dfree(h->d_TN); dfree(h->d_state[0]); dfree(h->d_state[1]); dfree(h->d_ticket);
+    if (h->h_flags) cudaFreeHost(h->h_flags);
+    if (h->h_readcnt) cudaFreeHost(h->h_readcnt);
+    if (h->h_lag) cudaFreeHost(h->h_lag);
+    if (h->h_mag) cudaFreeHost(h->h_mag);
+    if (h->h_phase) cudaFreeHost(h->h_phase);
+    if (h->h_meas) cudaFreeHost(h->h_meas);
+    for (int i = 0; i < 2; i++) if (h->h_packet[i]) cudaFreeHost(h->h_packet[i]);
+    for (auto ev : h->ev_in) cudaEventDestroy(ev);
+    for (auto ev : h->ev_done) cudaEventDestroy(ev);
+    if (h->ev_start) cudaEventDestroy(h->ev_start);
+    if (h->ev_out) cudaEventDestroy(h->ev_out);
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+extern "C" int cohcuda_register_host(cohcuda_t *h, void *p, size_t bytes) {
+    if (!h || !p || !bytes) return COHCUDA_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    h->registered.push_back(p);
+    return COHCUDA_OK;
+}
+
+extern "C" int cohcuda_unregister_host(cohcuda_t *h, void *p) {
+    if (!h || !p) return COHCUDA_ERR_ARG;
+    for (size_t i = 0; i < h->registered.size(); i++)
+        if (h->registered[i] == p) {
+            CK(cudaStreamSynchronize(h->stream));
+            CK(cudaHostUnregister(p));
+            h->registered.erase(h->registered.begin() + i);
+            return COHCUDA_OK;
+        }
+    h->err = "pointer was not registered";
+    return COHCUDA_ERR_ARG;
+}
+
+extern "C" int cohcuda_packet_layout(cohcuda_t *h, size_t *packet_len, size_t *dev_pitch, size_t *dev_lead) {
+    if (!h) return COHCUDA_ERR_ARG;
+    if (packet_len) *packet_len = h->plen;
+    if (dev_pitch) *dev_pitch = h->pitch;
+    if (dev_lead) *dev_lead = h->lead;
+    return COHCUDA_OK;
+}
+
+extern "C" int cohcuda_sync(cohcuda_t *h) {
+    if (!h) return COHCUDA_ERR_ARG;
+    CK(cudaStreamSynchronize(h->s_out));
+    CK(cudaStreamSynchronize(h->stream));
+    return COHCUDA_OK;
+}
+
+extern "C" uint64_t cohcuda_launch_count(cohcuda_t *h) { return h ? h->launches : 0; }
+extern "C" const int8_t *cohcuda_device_packets(cohcuda_t *h) { return h ? h->last_packets : nullptr; }
+
+extern "C" int cohcuda_get_state(cohcuda_t *h, cohcuda_chan_state *st, uint32_t n) {
+    if (!h || !st || n > h->nch) return COHCUDA_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<ChanState> tmp(n);
+    CK(cudaMemcpy(tmp.data(), h->d_state[h->cur], sizeof(ChanState) * n, cudaMemcpyDeviceToHost));
+    for (uint32_t i = 0; i < n; i++) {
+        st[i].phasecorr[0] = tmp[i].phasecorr.x; st[i].phasecorr[1] = tmp[i].phasecorr.y;
+        st[i].phasecorrprev[0] = tmp[i].phasecorrprev.x; st[i].phasecorrprev[1] = tmp[i].phasecorrprev.y;
+        st[i].lag = tmp[i].lag; st[i].mag = tmp[i].mag; st[i].held_lag = tmp[i].held_lag;
+    }
+    return COHCUDA_OK;
+}
+
+extern "C" int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uint32_t n) {
+    if (!h || !st || n > h->nch) return COHCUDA_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<ChanState> tmp(n);
+    for (uint32_t i = 0; i < n; i++) {
+        tmp[i].phasecorr = make_float2(st[i].phasecorr[0], st[i].phasecorr[1]);
+        tmp[i].phasecorrprev = make_float2(st[i].phasecorrprev[0], st[i].phasecorrprev[1]);
+        tmp[i].lag = st[i].lag; tmp[i].mag = st[i].mag; tmp[i].held_lag = st[i].held_lag; tmp[i].pad = 0;
+    }
+    CK(cudaMemcpy(h->d_state[h->cur], tmp.data(), sizeof(ChanState) * n, cudaMemcpyHostToDevice));
+    return COHCUDA_OK;
+}
+
+#include "api_batch.inc"
+#include "api_prims.inc"

@@ -1,0 +1,66 @@
+// kernels.h -- internal launch interfaces shared by the .cu files of libcoherent_cuda.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace coh {
+
+struct PeakRec { uint32_t idx; float val; };      // arg-max bin and |c|^2 there (ccoherent.cc:192,203)
+
+struct ChanState {                                // device mirror of cohcuda_chan_state
+    float2  phasecorr, phasecorrprev;
+    float   lag, mag;
+    int32_t held_lag;
+    int32_t pad;
+};
+
+struct CorrLaunch {
+    const uint8_t *iq; uint32_t nch, B;
+    uint32_t n_ref_blocks; const uint32_t *ref_block_list;   // blocks whose ref spectrum is needed (NULL = 0..n-1)
+    uint32_t n_items; const uint32_t *item_list;             // b*nch+c items (NULL = all signal channels of all blocks)
+    const uint32_t *block_slot;                              // block -> refspec slot (NULL = identity)
+    uint32_t xormask;
+    const float2 *TN; float2 *refspec; PeakRec *peaks;
+};
+cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st);
+bool correlate_supported(uint32_t B);
+
+struct ApplyLaunch {
+    const uint8_t *iq; uint32_t nch, B, n_blocks;     // n_blocks = whole batch (for the state hand-over)
+    uint32_t block0, n_launch_blocks;                  // blocks [block0, block0+n_launch_blocks) in this launch
+    uint32_t xormask;               // 0x80808080 for offset-binary input, 0 if already signed
+    int apply_shift, noheader;
+    float alpha; int lookback;      // IIR weight and look-back depth (enabled blocks)
+    // lag source: src_block[b*nch+c] = block whose peak applies (-1 = carried state); NULL with
+    // lag_all=1 means "own block", NULL with lag_all=0 means "carried state"
+    const int32_t *src_block; int lag_all;
+    const PeakRec *peaks;
+    const uint8_t *refnoise; int refnoise_scalar;            // per-block enable flags or scalar
+    const uint32_t *readcnt; uint32_t readcnt0, globalseqn0;
+    const ChanState *state_in; ChanState *state_out;
+    int8_t *packets; size_t pitch, lead;                     // device packet layout
+    float *lag, *mag; float2 *phase; uint8_t *measured;      // per (block, channel) outputs
+    float2 *cf32;                                            // optional corrected float matrix
+    // look-back scratch
+    float2 *q; uint32_t *flag; int2 *partial; uint32_t *pflag; uint32_t epoch;
+    uint32_t *ticket; uint32_t ticket0;     // device counter and its value at launch
+    int sm_count;
+};
+cudaError_t launch_apply(const ApplyLaunch &p, cudaStream_t st);
+uint32_t apply_parts(uint32_t B);                          // 16 KiB parts per channel-block
+
+// cdsp primitive kernels (device pointers)
+cudaError_t prim_convtosigned(const uint8_t *in, uint8_t *out, int n, cudaStream_t st);
+cudaError_t prim_convtofloat(float *out, const int8_t *in, int n, cudaStream_t st);
+cudaError_t prim_convto8bit(int8_t *out, const float *in, int nfloats, cudaStream_t st);
+cudaError_t prim_scalarmul(float2 *out, const float2 *in, float2 s, int n, cudaStream_t st);
+cudaError_t prim_conj_dot(float2 *res, const float2 *a, const float2 *b, int n, cudaStream_t st);
+cudaError_t prim_magsquared(float *out, const float2 *in, int n, cudaStream_t st);
+cudaError_t prim_conjugatemul(float2 *out, const float2 *a, const float2 *b, int n, cudaStream_t st);
+cudaError_t prim_indexofmax(uint32_t *idx, const float *in, int n, cudaStream_t st);
+cudaError_t prim_sumsq(float *res, const float *in, int n, cudaStream_t st);
+cudaError_t prim_fft(float2 *out, const float2 *in, int n, int howmany, int sign, const float2 *TN_n, cudaStream_t st);
+bool prim_fft_supported(int n);
+
+}  // namespace coh

@@ -1,0 +1,164 @@
+/*
+ * coherent_cuda.h -- C ABI of libcoherent_cuda.so: the block synchronisation + correction
+ * path of coherent-rtlsdr as hand-written sm_100a CUDA.
+ *
+ * The reference has no FFI: its seam is the C++ class surface of cdsp / ccoherent /
+ * cpacketize / csdrdevice.  Each entry point below names the reference code it replaces
+ * (file:line in the reference tree); the drop-in C++ classes in coherent-rtlsdr_b200/host/
+ * and INTEGRATION.md show the call sites a maintainer would change.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a
+ * negative cohcuda_status; nothing throws across the boundary (the reference's DSP path uses
+ * int returns and no exceptions, src/crtlsdr.cc:112-135); messages via cohcuda_last_error().
+ * One producer thread per handle (the reference has exactly one DSP thread,
+ * src/ccoherent.cc:296-298); handles are independent (one per GPU rank).
+ * There is no CPU fallback: without a usable CUDA device cohcuda_create() fails.
+ */
+#ifndef COHERENT_CUDA_H
+#define COHERENT_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cohcuda cohcuda_t;
+
+typedef enum {
+    COHCUDA_OK = 0,
+    COHCUDA_ERR_ARG = -1,        /* bad argument / unsupported size          */
+    COHCUDA_ERR_CUDA = -2,       /* CUDA runtime error (see last_error)      */
+    COHCUDA_ERR_NOMEM = -3,
+    COHCUDA_ERR_STATE = -4,      /* wait without submit, etc.                */
+    COHCUDA_ERR_UNSUPPORTED = -5
+} cohcuda_status;
+
+/* lag_mode for cohcuda_batch / meaning of lag_request == NULL */
+#define COHCUDA_LAG_NONE 0   /* TRACK: nobody requests a lag (reference steady state)        */
+#define COHCUDA_LAG_ALL  1   /* SYNC: every signal channel requests a lag in every block     */
+
+typedef struct {
+    uint32_t n_signal;          /* C, signal channels; the reference channel is extra         */
+    uint32_t blocksize;         /* B bytes per channel-block = 2L, power of two, 64..16384 for
+                                   the correlation path (src/main.cc:167 default 1<<14)       */
+    uint32_t max_lag_slots;     /* reference: nfft-1 = 7 (src/ccoherent.cc:124); 0 = no cap   */
+    float    alpha;             /* phase IIR weight; reference 0.5 (src/csdrdevice.cc:60)     */
+    int      noheader;          /* -R raw packets (src/cpacketizer.cc:91-96)                  */
+    int      apply_shift;       /* 1: software integer-delay removal; 0: as ref   */
+    int      device;            /* CUDA device ordinal                                        */
+    uint32_t max_batch_blocks;  /* capacity hint for cohcuda_batch (grows on demand)          */
+    void    *stream;            /* cudaStream_t to enqueue on, or NULL for a private stream   */
+} cohcuda_config;
+
+/* per-channel state that survives across blocks (include/csdrdevice.h:74-89) */
+typedef struct {
+    float   phasecorr[2];       /* csdrdevice::phasecorr                                      */
+    float   phasecorrprev[2];   /* csdrdevice::phasecorrprev                                  */
+    float   lag;                /* lagpoint.lag (include/csdrdevice.h:42-54)                  */
+    float   mag;                /* lagpoint.mag                                               */
+    int32_t held_lag;           /* integer lag applied while no new measurement arrives       */
+} cohcuda_chan_state;
+
+/* replaces ccoherent::ccoherent buffer/plan set-up (src/ccoherent.cc:32-95) and
+ * csdrdevice::csdrdevice state init (src/csdrdevice.cc:20-48) */
+int  cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out);
+/* replaces ccoherent::~ccoherent (src/ccoherent.cc:97-113) */
+void cohcuda_destroy(cohcuda_t *h);
+const char *cohcuda_last_error(cohcuda_t *h);   /* h may be NULL: last create() failure */
+
+/* pins librtlsdr-owned USB buffers so block copies are asynchronous; the zero-copy ring of
+ * include/common.h:114-122 (USELIBRTLSDRBUFS) hands exactly these pointers to the DSP thread */
+int cohcuda_register_host(cohcuda_t *h, void *p, size_t bytes);
+int cohcuda_unregister_host(cohcuda_t *h, void *p);
+
+/* packet geometry: packet_len = bytes of one packet as written by cpacketize::write
+ * (src/cpacketizer.cc:137-172): [hdr0 16][readcnt 4(C+1)][(C+1) columns x B] (hdr omitted with
+ * noheader).  On the device, packet b of a batch starts at base + b*dev_pitch + dev_lead so
+ * that every column is 16-byte aligned; host-side packets are contiguous (pitch packet_len). */
+int cohcuda_packet_layout(cohcuda_t *h, size_t *packet_len, size_t *dev_pitch, size_t *dev_lead);
+
+typedef struct {
+    const float  *lag;          /* C+1 floats (entry 0 = 0): lagpoint.lag per channel         */
+    const float  *mag;          /* C+1 floats: lagpoint.mag                                   */
+    const float  *phasecorr;    /* 2(C+1) floats: csdrdevice::get_phasecorrect(), what
+                                   cpacketize::writedebug publishes (cpacketizer.cc:131-134)  */
+    const uint8_t *measured;    /* C+1 flags: 1 where set_lag() would have fired this block   */
+    const int8_t *packet;       /* library-owned pinned host memory, valid until the
+                                   second-next submit (mirrors packetbuf0/1)                  */
+    size_t        packet_len;
+    uint32_t      globalseqn;
+} cohcuda_result;
+
+/*
+ * One block through the schedule of ccoherent::threadf (src/ccoherent.cc:245-294): convert
+ * (crtlsdr.cc:205-218), queue + correlate the channels whose lag_request flag is set
+ * (ccoherent.cc:123-152,154-239), estimate/apply phase (csdrdevice.cc:58-84), pack into the
+ * packet (cpacketizer.cc:137-172).  chan[0] = reference, chan[1..C] = signal; each B bytes,
+ * caller-owned, must stay valid until cohcuda_wait_block returns (the reference consume()s
+ * right after use, ccoherent.cc:254,281).  input_is_signed = 1 if the in-place XOR of
+ * cbuffer::setbufferptr (include/common.h:121) already ran on the buffers.
+ * Asynchronous: returns after enqueueing.
+ */
+int cohcuda_submit_block(cohcuda_t *h, const uint8_t *const *chan, const uint32_t *readcnt,
+                         const uint8_t *lag_request, int refnoise_enabled, int input_is_signed);
+/* blocks until the submitted block is done; replaces the tail of threadf up to notifysend()
+ * (ccoherent.cc:284-288) and fills what set_lag() publishes (csdrdevice.h:138-151) */
+int cohcuda_wait_block(cohcuda_t *h, cohcuda_result *r);
+
+typedef struct {
+    const uint8_t *iq;            /* [n_blocks][C+1][B] raw bytes                             */
+    int            iq_on_device;  /* 1: iq is a device pointer (16-byte aligned)              */
+    uint32_t       n_blocks;
+    const uint8_t *lag_request;   /* host [n_blocks][C+1] flags, or NULL -> lag_mode          */
+    int            lag_mode;      /* COHCUDA_LAG_NONE / COHCUDA_LAG_ALL                       */
+    const uint8_t *refnoise;      /* host [n_blocks] crefnoise::isenabled() per block or NULL */
+    int            refnoise_enabled; /* used when refnoise == NULL                            */
+    int            input_is_signed;
+    const uint32_t *readcnt;      /* host [n_blocks][C+1] or NULL -> readcnt0 + block         */
+    uint32_t       readcnt0;
+    uint32_t       globalseqn0;   /* hdr0.globalseqn of block 0 (cpacketizer.cc:113)          */
+    int8_t        *packets;       /* out: host (contiguous, packet_len pitch) or device
+                                     (dev_pitch/dev_lead layout); NULL = keep internal        */
+    int            packets_on_device;
+    float         *lag;           /* out, host [n_blocks][C+1] or NULL                        */
+    float         *mag;           /* out, host [n_blocks][C+1] or NULL                        */
+    float         *phasecorr;     /* out, host [n_blocks][C+1][2] or NULL                     */
+    float         *cf32;          /* out, DEVICE [n_blocks][C+1][L][2] corrected float matrix
+                                     (column 0 = converted ref) or NULL                       */
+} cohcuda_batch_args;
+
+/* Offline / bench entry: the same per-block schedule over n_blocks consecutive blocks, state
+ * carried from block to block exactly as a sequence of submit/wait calls would.  Enqueues on
+ * the handle's stream and returns; cohcuda_sync() waits. */
+int cohcuda_batch(cohcuda_t *h, const cohcuda_batch_args *a);
+int cohcuda_sync(cohcuda_t *h);
+/* kernels launched by this handle so far (bench.py reports it as gpu_launches) */
+uint64_t cohcuda_launch_count(cohcuda_t *h);
+/* device pointer of the internal packet buffer of the last batch (dev_pitch layout) */
+const int8_t *cohcuda_device_packets(cohcuda_t *h);
+
+/* checkpoint / restore of the per-channel state; n = C+1 entries */
+int cohcuda_get_state(cohcuda_t *h, cohcuda_chan_state *st, uint32_t n);
+int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uint32_t n);
+
+/* ---- cdsp primitives on host buffers (include/cdsp.h:36-71), each one kernel ---------- */
+/* every call copies in, runs the kernel, copies out and synchronises: a drop-in for code
+ * that calls cdsp:: directly, not the fast path.  h supplies device + stream.              */
+int cohcuda_cdsp_convtosigned(cohcuda_t *h, const uint8_t *in, uint8_t *out, int n);            /* cdsp.cc:21-34  */
+int cohcuda_cdsp_convtofloat(cohcuda_t *h, float *out, const int8_t *s8, int n);                /* cdsp.cc:36-44  */
+int cohcuda_cdsp_convto8bit(cohcuda_t *h, int8_t *out, const float *in, int n_complex);         /* cdsp.cc:51-54  */
+int cohcuda_cdsp_scalarmul(cohcuda_t *h, float *out, const float *in, float s_re, float s_im, int n); /* cdsp.cc:46-49 */
+int cohcuda_cdsp_conj_dotproduct(cohcuda_t *h, float *res2, const float *a, const float *b, int n);   /* cdsp.cc:61-66 */
+int cohcuda_cdsp_magsquared(cohcuda_t *h, float *out, const float *in, int n);                  /* cdsp.cc:100-103 */
+int cohcuda_cdsp_conjugatemul(cohcuda_t *h, float *out, const float *a, const float *b, int n); /* cdsp.cc:105-108 */
+int cohcuda_cdsp_indexofmax(cohcuda_t *h, uint32_t *idx, const float *in, int n);               /* cdsp.cc:135-139 */
+int cohcuda_cdsp_rms(cohcuda_t *h, float *res, const float *in, int n);                         /* cdsp.cc:68-73  */
+/* batched c2c DFT, n a power of two (32..16384), sign -1 forward / +1 backward, unnormalised:
+ * fftwf_plan_many_dft + fftwf_execute_dft as used at src/ccoherent.cc:87-93,174,182 */
+int cohcuda_cdsp_fft(cohcuda_t *h, float *out, const float *in, int n, int howmany, int sign);  /* cdsp.cc:110-120 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

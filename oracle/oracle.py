@@ -1,0 +1,152 @@
+"""ctypes front-end for oracle/liboracle.so plus an independent numpy restatement.
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs -- never by the product package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liboracle.so")
+REF_LIB_PATH = os.path.join(HERE, "_ref", "libref_cdsp.so")
+
+
+class Cf32(C.Structure):
+    _fields_ = [("re", C.c_float), ("im", C.c_float)]
+
+
+class OrcConfig(C.Structure):
+    _fields_ = [("n_signal", C.c_uint32), ("blocksize", C.c_uint32), ("alpha", C.c_float),
+                ("noheader", C.c_int), ("apply_shift", C.c_int), ("int_dot", C.c_int),
+                ("max_lag_slots", C.c_int)]
+
+
+class OrcChanState(C.Structure):
+    _fields_ = [("phasecorr", Cf32), ("phasecorrprev", Cf32), ("lag", C.c_float),
+                ("mag", C.c_float), ("held_lag", C.c_int32)]
+
+
+def build(force: bool = False) -> None:
+    """Compile liboracle.so (and _ref when /root/reference is present)."""
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-s", "-C", HERE, LIB_PATH])
+    subprocess.call(["make", "-s", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        vp, u32, i = C.c_void_p, C.c_uint32, C.c_int
+        L.orc_packet_len.restype = C.c_size_t
+        L.orc_packet_len.argtypes = [C.POINTER(OrcConfig)]
+        L.orc_state_init.argtypes = [vp, u32]
+        L.orc_process_batch.argtypes = [C.POINTER(OrcConfig), vp, vp, u32, vp, i, vp, i, u32,
+                                        vp, vp, vp, vp, vp]
+        L.orc_computelag_pair.argtypes = [vp, vp, u32, vp, vp, vp, vp]
+        L.orc_fft.argtypes = [vp, vp, i, i]
+        L.orc_convtosigned.argtypes = [vp, vp, i]
+        L.orc_convtofloat.argtypes = [vp, vp, i]
+        L.orc_convto8bit.argtypes = [vp, vp, i]
+        L.orc_scalarmul.argtypes = [vp, vp, Cf32, i]
+        L.orc_conj_dotproduct.argtypes = [vp, vp, i]
+        L.orc_conj_dotproduct.restype = Cf32
+        L.orc_magsquared.argtypes = [vp, vp, i]
+        L.orc_conjugatemul.argtypes = [vp, vp, vp, i]
+        L.orc_indexofmax.argtypes = [vp, i]
+        L.orc_indexofmax.restype = C.c_uint32
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def make_config(n_signal, blocksize, alpha=0.5, noheader=0, apply_shift=0, int_dot=0,
+                max_lag_slots=0):
+    return OrcConfig(n_signal, blocksize, alpha, noheader, apply_shift, int_dot, max_lag_slots)
+
+
+def new_state(n_chan):
+    st = (OrcChanState * n_chan)()
+    lib().orc_state_init(st, n_chan)
+    return st
+
+
+def process_batch(cfg, iq, state=None, lag_request=None, lag_mode=1, refnoise=None,
+                  input_is_signed=0, readcnt0=0, want_cf32=False):
+    """Run orc_process_batch.  iq: uint8 [n_blocks][C+1][B].  Returns dict of numpy arrays."""
+    iq = np.ascontiguousarray(iq, dtype=np.uint8)
+    nb, nch, B = iq.shape
+    assert nch == cfg.n_signal + 1 and B == cfg.blocksize
+    st = state if state is not None else new_state(nch)
+    plen = lib().orc_packet_len(C.byref(cfg))
+    packets = np.zeros((nb, plen), dtype=np.int8)
+    lag = np.zeros((nb, nch), dtype=np.float32)
+    mag = np.zeros((nb, nch), dtype=np.float32)
+    phase = np.zeros((nb, nch), dtype=np.complex64)
+    cf = np.zeros((nb, nch, B // 2), dtype=np.complex64) if want_cf32 else None
+    lr = None if lag_request is None else np.ascontiguousarray(lag_request, dtype=np.uint8)
+    rn = None if refnoise is None else np.ascontiguousarray(refnoise, dtype=np.uint8)
+    lib().orc_process_batch(C.byref(cfg), st, _p(iq), nb, _p(lr), int(lag_mode), _p(rn),
+                            int(input_is_signed), int(readcnt0), _p(packets), _p(lag), _p(mag),
+                            _p(phase), _p(cf))
+    return {"packets": packets, "lag": lag, "mag": mag, "phase": phase, "cf32": cf, "state": st}
+
+
+def computelag_pair(x, r):
+    x = np.ascontiguousarray(x, dtype=np.complex64)
+    r = np.ascontiguousarray(r, dtype=np.complex64)
+    idx = C.c_uint32(); lag = C.c_float(); mag = C.c_float(); margin = C.c_float()
+    lib().orc_computelag_pair(_p(x), _p(r), len(x), C.byref(idx), C.byref(lag), C.byref(mag),
+                              C.byref(margin))
+    return idx.value, lag.value, mag.value, margin.value
+
+
+def fft(x, sign=-1):
+    x = np.ascontiguousarray(x, dtype=np.complex64)
+    out = np.empty_like(x)
+    lib().orc_fft(_p(out), _p(x), len(x), sign)
+    return out
+
+
+# ----------------------------------------------------------------- numpy restatement -----
+# Independent cross-check of the C oracle (different FFT, float64 accumulation).
+
+def np_convtofloat(u8, input_is_signed=False):
+    """cdsp.cc:21-44: (u8 ^ 0x80) as int8, times float32(1/127)."""
+    s8 = (u8 if input_is_signed else (u8 ^ np.uint8(0x80))).view(np.int8)
+    return s8.astype(np.float32) * np.float32(1.0 / 127.0)
+
+
+def np_to_complex(f):
+    return f.reshape(f.shape[:-1] + (-1, 2)).view(np.complex64)[..., 0]
+
+
+def np_computelag(x, r):
+    """ccoherent.cc:154-239 with the crtlsdr.cc:205-218 buffer layout, in float64."""
+    L = len(x)
+    sx = np.zeros(2 * L, dtype=np.complex128); sx[:L] = x
+    sr = np.zeros(2 * L, dtype=np.complex128); sr[L:] = r
+    c = np.fft.ifft(np.fft.fft(sx) * np.conj(np.fft.fft(sr))) * (2 * L)
+    m = (c.real ** 2 + c.imag ** 2)
+    idx = int(np.argmax(m))
+    return idx, float(idx - L), float(np.sqrt(m[idx] / L)), c
+
+
+def np_pack8(v):
+    """cdsp.cc:51-54 / volk_32f_s32f_convert_8i: clamp(rint(127*v))."""
+    r = (v.astype(np.float32) * np.float32(127.0))
+    r = np.clip(r, np.float32(-128.0), np.float32(127.0))
+    return np.rint(r).astype(np.int8)
