@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""bench.py -- coherent samples/s of the block sync + correction path on synthetic IQ.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--mode sync|track] [--impl reference]
+
+One "step" = one pass of the hot path over one batch: URA21 geometry (21 signal + 1 reference
+channel, 8192-sample blocks, 1024 blocks = BASELINE.json configs[1]).  `value` = coherent samples/s
+((C+1)*L*blocks / time, every column of the emitted matrix counts) with the input already in HBM;
+`e2e` = the same through cohcuda_batch with pinned HOST buffers (H2D + kernels + D2H timed).
+N > 1 (torchrun): one process per GPU, each rank runs its own shard of blocks with its own copy of
+the reference channel (weak scaling, no data-path collective in `value`); `with_gather` adds the
+NCCL gather of the packed matrix to rank 0.
+`--impl reference` times the reference's CPU path (oracle/_ref when built, else the oracle port)
+on the host cores for the same metric.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+C_SIG, BLOCKSIZE, N_BLOCKS = 21, 16384, 1024
+BYTES_PER_SAMPLE = 4.0            # 2 B u8 IQ in + 2 B int8 IQ out (packet mode)
+FLOP_PER_SAMPLE_SYNC = 311.0      # SURVEY 8d algorithmic flops per coherent sample, SYNC mode
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64):
+    """Synthetic IQ of SURVEY 8d generated on the device (same model as synth.make_blocks)."""
+    L = blocksize // 2
+    g = torch.Generator(device=device); g.manual_seed(seed)
+    rng = np.random.Generator(np.random.PCG64(seed))
+    gains = rng.uniform(0.7, 1.0, n_signal); phases = rng.uniform(-np.pi, np.pi, n_signal)
+    delays = rng.integers(-max_delay, max_delay + 1, n_signal)
+    pad = max_delay + 1
+    T = n_blocks * L + 2 * pad
+    r = torch.randn(T, 2, generator=g, device=device) * 40.0
+    iq = torch.empty(n_blocks, n_signal + 1, blocksize, dtype=torch.uint8, device=device)
+
+    def quant(v):
+        return torch.clamp(torch.round(v + 127.5), 0, 255).to(torch.uint8)
+
+    iq[:, 0, :] = quant(r[pad:pad + n_blocks * L]).reshape(n_blocks, blocksize)
+    for k in range(n_signal):
+        s = pad - int(delays[k])
+        seg = r[s:s + n_blocks * L]
+        c, sn = float(gains[k] * np.cos(phases[k])), float(gains[k] * np.sin(phases[k]))
+        w = torch.randn(n_blocks * L, 2, generator=g, device=device) * 4.0
+        x = torch.stack((seg[:, 0] * c - seg[:, 1] * sn, seg[:, 0] * sn + seg[:, 1] * c), dim=1) + w
+        iq[:, k + 1, :] = quant(x).reshape(n_blocks, blocksize)
+    return iq, delays, phases
+
+
+# ------------------------------------------------------------------ CPU baseline / reference arm
+def cpu_pass(O, iq, mode, threads):
+    """One pass of the CPU path over iq[nb][C+1][B]; returns seconds.  threads > 1 splits the
+    blocks into contiguous ranges, one oracle state per range (SURVEY BASELINE B2)."""
+    nb, nch, B = iq.shape
+    cfg = O.make_config(nch - 1, B)
+    lag_mode = 1 if mode == "sync" else 0
+    ranges = [(i * nb // threads, (i + 1) * nb // threads) for i in range(threads)]
+    ranges = [r for r in ranges if r[1] > r[0]]
+
+    def work(r):
+        O.process_batch(cfg, iq[r[0]:r[1]], lag_mode=lag_mode)
+
+    t0 = time.perf_counter()
+    if len(ranges) == 1:
+        work(ranges[0])
+    else:
+        ts = [threading.Thread(target=work, args=(r,)) for r in ranges]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+    return time.perf_counter() - t0
+
+
+def cpu_kind(O):
+    return "reference" if getattr(O, "ref_available", lambda: False)() else "port"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import oracle as O
+    cohpkg = __import__("cohpkg")
+    synth = cohpkg.synth()
+    cores = os.cpu_count() or 1
+    mode = args.mode
+    # bounded sample of the workload: per step `sample_blocks` blocks of the URA21 geometry
+    sample_blocks = args.cpu_blocks or (2 * cores if mode == "sync" else 16 * cores)
+    iq, _ = synth.make_blocks(C_SIG, BLOCKSIZE, sample_blocks, seed=0xC0DE + 1)
+    for _ in range(args.warmup):
+        cpu_pass(O, iq[:max(cores, 1)], mode, cores)
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_pass(O, iq, mode, cores)
+    samples = (C_SIG + 1) * (BLOCKSIZE // 2) * sample_blocks * args.steps
+    v = samples / t
+    line = {
+        "impl": "reference", "metric": "coherent samples/sec", "value": v, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"URA21 {C_SIG}+1 ch x {BLOCKSIZE // 2} samples, {mode} mode, "
+                               f"CPU sample of {sample_blocks} blocks/step (full workload {N_BLOCKS})",
+                   "mode": mode},
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": cpu_kind(O),
+                         "sample": f"{sample_blocks} blocks x {C_SIG + 1} channels per step, {args.steps} steps, "
+                                   f"{cores} threads over contiguous block ranges"},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------ GPU arm
+def run_gpu_arm(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import cohpkg
+    pkg = cohpkg.load()
+    stream = torch.cuda.Stream(device=dev)
+    nb, nch, B, L = args.blocks, C_SIG + 1, BLOCKSIZE, BLOCKSIZE // 2
+    eng = pkg.CoherentCuda(C_SIG, B, apply_shift=True, device=local, max_batch_blocks=nb,
+                           stream=stream.cuda_stream)
+    # each rank holds its own shard of blocks and its own copy of the reference channel
+    iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev)
+    pk_dev = torch.zeros(nb * eng.dev_pitch + 16, dtype=torch.int8, device=dev)
+    torch.cuda.synchronize()
+    samples_per_step = nch * L * nb
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step_dev(mode):
+        eng.batch_raw(iq=iq.data_ptr(), iq_on_device=1, n_blocks=nb,
+                      lag_mode=pkg.LAG_ALL if mode == "sync" else pkg.LAG_NONE, refnoise_enabled=1,
+                      packets=pk_dev.data_ptr(), packets_on_device=1)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    hbm_peak, peak_src = measured_peaks()
+    sampler = ClockSampler(local)
+    # the acquisition pass leaves the measured lags held, so TRACK runs with real shifts applied
+    step_dev("sync"); eng.sync()
+    launches0 = eng.launch_count()
+    if rank == 0:
+        sampler.start()
+    ms_main = timed(lambda: step_dev(args.mode), args.steps, args.warmup)
+    launches = (eng.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    other = "track" if args.mode == "sync" else "sync"
+    ms_other = timed(lambda: step_dev(other), args.steps, args.warmup)
+
+    # per-kernel durations (CUDA events on the launching stream, one launch at a time)
+    def profile(mode):
+        eng.profile(True)
+        for _ in range(2):
+            step_dev(mode)
+        eng.sync()
+        p = eng.profile_read()
+        eng.profile(False)
+        return p
+    prof = {"sync": profile("sync"), "track": profile("track")}
+
+    def roofline(mode):
+        if mode == "sync":
+            k = prof["sync"]["k_correlate"]; units = 2 * C_SIG * nb * L      # two profiled steps
+            name = "k_correlate"
+        else:
+            k = prof["track"]["k_apply"]; units = 2 * nch * nb * L
+            name = "k_apply"
+        gbs = units * BYTES_PER_SAMPLE / (k["ms"] * 1e-3) / 1e9
+        r = {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+             "frac": gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+             "launches_timed": k["launches"], "avg_launch_ms": k["ms"] / max(k["launches"], 1),
+             "algorithmic_bytes_per_launch": units * BYTES_PER_SAMPLE / max(k["launches"], 1)}
+        if mode == "sync":
+            r["fp32_tflops_algorithmic"] = units * FLOP_PER_SAMPLE_SYNC / (k["ms"] * 1e-3) / 1e12
+        return r
+
+    # ---- end to end through the C ABI with pinned host buffers ------------------------------
+    h_iq = torch.empty((nb, nch, B), dtype=torch.uint8, pin_memory=True); h_iq.copy_(iq)
+    h_pk = torch.empty((nb, eng.packet_len), dtype=torch.int8, pin_memory=True)
+    h_lag = torch.empty((nb, nch), dtype=torch.float32, pin_memory=True)
+    h_mag = torch.empty((nb, nch), dtype=torch.float32, pin_memory=True)
+    h_ph = torch.empty((nb, nch, 2), dtype=torch.float32, pin_memory=True)
+
+    def step_e2e():
+        eng.batch_raw(iq=h_iq.data_ptr(), iq_on_device=0, n_blocks=nb,
+                      lag_mode=pkg.LAG_ALL if args.mode == "sync" else pkg.LAG_NONE, refnoise_enabled=1,
+                      packets=h_pk.data_ptr(), packets_on_device=0, lag=h_lag.data_ptr(),
+                      mag=h_mag.data_ptr(), phasecorr=h_ph.data_ptr())
+    ms_e2e = timed(step_e2e, max(args.steps // 2, 2), 3)
+    e2e_steps = max(args.steps // 2, 2)
+    lag_ok = bool((h_lag[:, 1:].numpy() == delays[None, :]).all()) if args.mode == "sync" else None
+
+    with_gather = None
+    if dist is not None:
+        glist = [torch.empty_like(pk_dev) for _ in range(world)] if rank == 0 else None
+
+        def step_gather():
+            step_dev(args.mode)
+            stream.synchronize()
+            dist.gather(pk_dev, glist, dst=0)
+        t0 = time.perf_counter(); barrier()
+        for _ in range(2):
+            step_gather()
+        barrier(); t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_gather()
+        barrier()
+        ms_g = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        with_gather = {"value": world * samples_per_step * args.steps / (ms_g * 1e-3), "unit": "samples/s",
+                       "collective": "NCCL gather of packed int8 packets to rank 0",
+                       "bytes_per_rank_per_step": int(pk_dev.numel())}
+
+    if rank == 0:
+        val = lambda ms, steps: world * samples_per_step * steps / (ms * 1e-3)
+        line = {
+            "metric": "coherent samples/sec", "value": val(ms_main, args.steps), "unit": "samples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_main / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"URA21: {C_SIG}+1 channels x {L}-sample blocks x {nb} blocks per GPU "
+                                   f"(BASELINE.json configs[1]), {args.mode.upper()} mode, software shift on",
+                       "mode": args.mode, "blocks_per_gpu": nb, "channels": nch, "L": L,
+                       "parallelism": f"block-sharded x{world}, ref channel replicated",
+                       "l2": f"input {nb * nch * B >> 20} MiB + output {nb * nch * B >> 20} MiB per step exceed the 126 MB L2 (no flush needed)"},
+            "roofline": roofline(args.mode),
+            "modes": {args.mode: {"value": val(ms_main, args.steps), "ms_per_step": ms_main / args.steps},
+                      other: {"value": val(ms_other, args.steps), "ms_per_step": ms_other / args.steps,
+                              "roofline": roofline(other)}},
+            "kernel_ms_per_step": {m: {k: v["ms"] / 2 for k, v in prof[m].items()} for m in prof},
+            "e2e": {"value": val(ms_e2e, e2e_steps), "unit": "samples/s",
+                    "h2d_bytes_per_step": world * int(h_iq.numel()),
+                    "d2h_bytes_per_step": world * int(h_pk.numel() + 4 * h_lag.numel() + 4 * h_mag.numel() + 4 * h_ph.numel()),
+                    "ms_per_step": ms_e2e / e2e_steps, "lag_known_answer_ok": lag_ok},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        if with_gather:
+            line["with_gather"] = with_gather
+        if world == 1 and not args.no_cpu:
+            from oracle import oracle as O
+            synth = cohpkg.synth()
+            probe, _ = synth.make_blocks(C_SIG, B, 8, seed=0xC0DE + 1)
+            t_probe = cpu_pass(O, probe, args.mode, 1)
+            n_cpu = int(min(max(8, 8 * args.cpu_seconds / max(t_probe, 1e-6)), 2048))
+            cpu_iq, _ = synth.make_blocks(C_SIG, B, n_cpu, seed=0xC0DE + 1)
+            t_cpu = cpu_pass(O, cpu_iq, args.mode, 1)
+            line["cpu_baseline"] = {"value": nch * L * n_cpu / t_cpu, "unit": "samples/s", "cores": 1,
+                                    "kind": cpu_kind(O),
+                                    "sample": f"{n_cpu} blocks x {nch} channels of the same workload, {args.mode} mode, "
+                                              f"1 thread (the reference's single DSP thread), {t_cpu:.1f} s"}
+        print(json.dumps(line))
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="sync", choices=["sync", "track"])
+    ap.add_argument("--blocks", type=int, default=N_BLOCKS)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--cpu-blocks", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -29,7 +29,7 @@ ABI_SYMBOLS = [
     "cohcuda_cdsp_convtosigned", "cohcuda_cdsp_convtofloat", "cohcuda_cdsp_convto8bit",
     "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
     "cohcuda_cdsp_conjugatemul", "cohcuda_cdsp_indexofmax", "cohcuda_cdsp_rms",
-    "cohcuda_cdsp_fft",
+    "cohcuda_cdsp_fft", "cohcuda_profile", "cohcuda_profile_read",
 ]
 
 
@@ -101,6 +101,8 @@ def load_library():
     L.cohcuda_cdsp_indexofmax.argtypes = [vp, vp, vp, i]
     L.cohcuda_cdsp_rms.argtypes = [vp, vp, vp, i]
     L.cohcuda_cdsp_fft.argtypes = [vp, vp, vp, i, i, i]
+    L.cohcuda_profile.argtypes = [vp, i]
+    L.cohcuda_profile_read.argtypes = [vp, vp, vp]
     _lib = L
     return L
 
@@ -216,6 +218,15 @@ class CoherentCuda:
 
     def set_state(self, st):
         self._check(self.lib.cohcuda_set_state(self.h, st, self.nch), "cohcuda_set_state")
+
+    def profile(self, enable):
+        self._check(self.lib.cohcuda_profile(self.h, int(enable)), "cohcuda_profile")
+
+    def profile_read(self):
+        ms = (C.c_double * 3)(); n = (C.c_uint32 * 3)()
+        self._check(self.lib.cohcuda_profile_read(self.h, ms, n), "cohcuda_profile_read")
+        names = ("k_ref_spectrum", "k_correlate", "k_apply")
+        return {k: {"ms": ms[i], "launches": n[i]} for i, k in enumerate(names)}
 
     def launch_count(self):
         return int(self.lib.cohcuda_launch_count(self.h))

@@ -45,6 +45,9 @@ struct cohcuda {
     std::vector<cudaEvent_t> ev_in, ev_done;
     cudaEvent_t ev_start = nullptr, ev_out = nullptr;
     std::vector<void *> registered;
+    // optional per-kernel timing (cohcuda_profile): 0 = k_ref_spectrum, 1 = k_correlate, 2 = k_apply
+    bool prof = false; cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+    double prof_ms[3] = { 0, 0, 0 }; uint32_t prof_n[3] = { 0, 0, 0 };
 };
 
 static constexpr uint32_t kCorrChunk = 148;             // blocks per K1/K2 launch: items = 148*C
@@ -197,6 +200,8 @@ extern "C" void cohcuda_destroy(cohcuda_t *h) {
     for (auto ev : h->ev_done) cudaEventDestroy(ev);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_out) cudaEventDestroy(h->ev_out);
+    if (h->pe0) cudaEventDestroy(h->pe0);
+    if (h->pe1) cudaEventDestroy(h->pe1);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -267,6 +272,31 @@ extern "C" int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uin
         tmp[i].lag = st[i].lag; tmp[i].mag = st[i].mag; tmp[i].held_lag = st[i].held_lag; tmp[i].pad = 0;
     }
     CK(cudaMemcpy(h->d_state[h->cur], tmp.data(), sizeof(ChanState) * n, cudaMemcpyHostToDevice));
+    return COHCUDA_OK;
+}
+
+// run one launch, optionally bracketed by events on the launching stream (profile mode syncs)
+template <typename F> static int timed_launch(cohcuda *h, int which, F &&f) {
+    if (!h->prof) { CK(f()); h->launches++; return COHCUDA_OK; }
+    if (!h->pe0) { CK(cudaEventCreate(&h->pe0)); CK(cudaEventCreate(&h->pe1)); }
+    CK(cudaEventRecord(h->pe0, h->stream));
+    CK(f());
+    CK(cudaEventRecord(h->pe1, h->stream));
+    CK(cudaEventSynchronize(h->pe1));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, h->pe0, h->pe1));
+    h->prof_ms[which] += ms; h->prof_n[which]++; h->launches++;
+    return COHCUDA_OK;
+}
+
+extern "C" int cohcuda_profile(cohcuda_t *h, int enable) {
+    if (!h) return COHCUDA_ERR_ARG;
+    h->prof = enable != 0;
+    for (int i = 0; i < 3; i++) { h->prof_ms[i] = 0; h->prof_n[i] = 0; }
+    return COHCUDA_OK;
+}
+extern "C" int cohcuda_profile_read(cohcuda_t *h, double *ms3, uint32_t *launches3) {
+    if (!h || !ms3 || !launches3) return COHCUDA_ERR_ARG;
+    for (int i = 0; i < 3; i++) { ms3[i] = h->prof_ms[i]; launches3[i] = h->prof_n[i]; }
     return COHCUDA_OK;
 }
 

@@ -135,6 +135,11 @@ int cohcuda_batch(cohcuda_t *h, const cohcuda_batch_args *a);
 int cohcuda_sync(cohcuda_t *h);
 /* kernels launched by this handle so far (bench.py reports it as gpu_launches) */
 uint64_t cohcuda_launch_count(cohcuda_t *h);
+/* per-kernel timing for bench.py's roofline line: while enabled every launch is bracketed by
+ * CUDA events on the launching stream and synchronised (a measurement mode, not the fast path).
+ * ms3 / launches3 index: 0 = k_ref_spectrum, 1 = k_correlate, 2 = k_apply */
+int cohcuda_profile(cohcuda_t *h, int enable);
+int cohcuda_profile_read(cohcuda_t *h, double *ms3, uint32_t *launches3);
 /* device pointer of the internal packet buffer of the last batch (dev_pitch layout) */
 const int8_t *cohcuda_device_packets(cohcuda_t *h);
 
