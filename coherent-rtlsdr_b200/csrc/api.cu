@@ -32,7 +32,7 @@ struct cohcuda {
     uint8_t *d_iq = nullptr; int8_t *d_packets = nullptr;
     float2 *d_refspec = nullptr; PeakRec *d_peaks = nullptr;
     float *d_lag = nullptr, *d_mag = nullptr; float2 *d_phase = nullptr; uint8_t *d_meas = nullptr;
-    float2 *d_q = nullptr; uint32_t *d_flag = nullptr; int2 *d_partial = nullptr; uint32_t *d_pflag = nullptr;
+    uint4 *d_q = nullptr, *d_partial = nullptr;
     int32_t *d_src = nullptr; uint32_t *d_items = nullptr, *d_reflist = nullptr, *d_slot = nullptr;
     uint8_t *d_refnoise = nullptr; uint32_t *d_readcnt = nullptr;
     const int8_t *last_packets = nullptr;
@@ -71,7 +71,7 @@ template <typename T> static void dfree(T *&p) { if (p) cudaFree(p); p = nullptr
 static void free_batch_buffers(cohcuda *h) {
     dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_refspec); dfree(h->d_peaks);
     dfree(h->d_lag); dfree(h->d_mag); dfree(h->d_phase); dfree(h->d_meas);
-    dfree(h->d_q); dfree(h->d_flag); dfree(h->d_partial); dfree(h->d_pflag);
+    dfree(h->d_q); dfree(h->d_partial);
     dfree(h->d_src); dfree(h->d_items); dfree(h->d_reflist); dfree(h->d_slot);
     dfree(h->d_refnoise); dfree(h->d_readcnt);
     h->cap = 0;
@@ -88,8 +88,7 @@ static int ensure_capacity(cohcuda *h, uint32_t nb) {
         CK(dalloc(&h->d_refspec, (size_t)kCorrChunk * 2 * h->L));
     CK(dalloc(&h->d_peaks, n));
     CK(dalloc(&h->d_lag, n)); CK(dalloc(&h->d_mag, n)); CK(dalloc(&h->d_phase, n)); CK(dalloc(&h->d_meas, n));
-    CK(dalloc(&h->d_q, n)); CK(dalloc(&h->d_flag, n));
-    CK(dalloc(&h->d_partial, n * parts)); CK(dalloc(&h->d_pflag, n * parts));
+    CK(dalloc(&h->d_q, n)); CK(dalloc(&h->d_partial, n * parts));
     CK(dalloc(&h->d_src, n)); CK(dalloc(&h->d_items, n)); CK(dalloc(&h->d_reflist, (size_t)nb)); CK(dalloc(&h->d_slot, (size_t)nb));
     CK(dalloc(&h->d_refnoise, (size_t)nb)); CK(dalloc(&h->d_readcnt, n));
     h->cap = nb;

@@ -20,6 +20,11 @@
 // p_b = alpha*q_b + (1-alpha)*p_(b-1) couples consecutive blocks of a channel; each item
 // publishes its raw estimate q_b and evaluates the recurrence over the previous `lookback`
 // published estimates (decoupled look-back; the truncated tail weighs (1-alpha)^lookback).
+// A published record is ONE aligned 16-byte word {q.re, q.im, epoch, check}: value and ready
+// flag travel in a single transaction, so no fence (and no L1 invalidation) is needed.
+//
+// Arithmetic runs two samples at a time on Blackwell's packed fp32 pipe (FADD2/FMUL2/FFMA2)
+// with the real parts of a word in one register pair and the imaginary parts in the other.
 #include "kernels.h"
 
 namespace coh {
@@ -29,70 +34,77 @@ constexpr int kChunksPerThread = 4;                       // 4 x 16 B = 64 B of 
 constexpr uint32_t kPartBytes = kApplyThreads * kChunksPerThread * 16;   // 16 KiB
 constexpr int kMaxLookback = 2048;
 
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+// ---- 16-byte publish / poll ------------------------------------------------------------------
+__device__ __forceinline__ void publish16(uint4 *p, uint32_t a, uint32_t b, uint32_t epoch) {
+    uint32_t chk = a ^ b ^ epoch ^ 0x5bd1e995u;
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(p), "r"(a), "r"(b), "r"(epoch), "r"(chk) : "memory");
 }
-__device__ __forceinline__ void st_release(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// 16 bytes of x'[n] = x[n + sh] (raw domain, zero_code outside the block); j = 16-byte chunk
-// index inside the channel-block
-__device__ __forceinline__ uint4 load_x_chunk(const uint8_t *x, int j, int sh, uint32_t B, uint32_t zero_code) {
-    uint4 r;
-    if ((sh & 7) == 0) {
-        int jj = j + (sh >> 3);
-        if (jj >= 0 && jj < (int)(B >> 4)) r = __ldg(reinterpret_cast<const uint4 *>(x) + jj);
-        else r = make_uint4(zero_code, zero_code, zero_code, zero_code);
-    } else {
-        const int o = 16 * j + 2 * sh;                   // byte offset, may be negative
-        const int w0 = o >> 2, sub = o & 3;              // arithmetic shift = floor
-        uint32_t w[5];
-#pragma unroll
-        for (int i = 0; i < 5; i++) {
-            int idx = w0 + i;
-            w[i] = (idx >= 0 && idx < (int)(B >> 2)) ? __ldg(reinterpret_cast<const uint32_t *>(x) + idx) : zero_code;
-        }
-        if (sub) {
-            r.x = __funnelshift_r(w[0], w[1], 16); r.y = __funnelshift_r(w[1], w[2], 16);
-            r.z = __funnelshift_r(w[2], w[3], 16); r.w = __funnelshift_r(w[3], w[4], 16);
-        } else { r.x = w[0]; r.y = w[1]; r.z = w[2]; r.w = w[3]; }
+__device__ __forceinline__ uint4 poll16(const uint4 *p, uint32_t epoch) {
+    uint4 v;
+    for (;;) {
+        asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        if (v.z == epoch && v.w == (v.x ^ v.y ^ epoch ^ 0x5bd1e995u)) return v;
+        __nanosleep(40);
     }
-    return r;
 }
 
-// exact (float)int8 * float(1/127) of byte k of the offset-binary word xu
-// (cdsp::convtofloat, src/cdsp.cc:41-44: volk multiplies by the rounded reciprocal)
-template <int K>
-__device__ __forceinline__ float byte_to_float(uint32_t xu) {
-    float f = __uint_as_float(__byte_perm(xu, 0x4B000000u, 0x7440 | K));     // 2^23 + u8
-    return __fmul_rn(f - 8388736.0f, 0x1.020408p-7f);                          // (u8 - 128) / 127
+// ---- shifted load: 16 bytes of x'[n] = x[n + sh] (raw domain, zero_code outside the block) ---
+// j = 16-byte chunk index inside the channel-block.  The byte offset 16*j + 2*sh has the same
+// residue mod 16 for every chunk, so the word select below is uniform across the CTA.
+__device__ __forceinline__ uint4 load_x_chunk(const uint4 *x4, int j, int sh, int nchunks, uint32_t zero_code) {
+    const uint4 z = make_uint4(zero_code, zero_code, zero_code, zero_code);
+    const int o = 16 * j + 2 * sh;                       // may be negative
+    const int a = o >> 4, rem = o & 15;                  // arithmetic shift = floor
+    uint4 A = (a >= 0 && a < nchunks) ? __ldg(x4 + a) : z;
+    if (rem == 0) return A;
+    uint4 Bv = (a + 1 >= 0 && a + 1 < nchunks) ? __ldg(x4 + a + 1) : z;
+    uint32_t w0, w1, w2, w3, w4;
+    switch (rem >> 2) {
+        case 0:  w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = Bv.x; break;
+        case 1:  w0 = A.y; w1 = A.z; w2 = A.w; w3 = Bv.x; w4 = Bv.y; break;
+        case 2:  w0 = A.z; w1 = A.w; w2 = Bv.x; w3 = Bv.y; w4 = Bv.z; break;
+        default: w0 = A.w; w1 = Bv.x; w2 = Bv.y; w3 = Bv.z; w4 = Bv.w; break;
+    }
+    if (rem & 2)
+        return make_uint4(__funnelshift_r(w0, w1, 16), __funnelshift_r(w1, w2, 16),
+                          __funnelshift_r(w2, w3, 16), __funnelshift_r(w3, w4, 16));
+    return make_uint4(w0, w1, w2, w3);
 }
 
-// volk_32f_s32f_convert_8i (src/cdsp.cc:51-54): clamp(v*127) to [-128,127], round half even
-__device__ __forceinline__ uint32_t float_to_s8_bits(float y) {
-    float v = __fmul_rn(y, 127.0f);
-    v = fminf(fmaxf(v, -128.0f), 127.0f);
-    return __float_as_uint(__fadd_rn(v, 12582912.0f));   // low byte = rint(v) two's complement
+// ---- one 32-bit word = two complex samples ----------------------------------------------------
+struct RotConst { float2 px, py, npy; };    // (p.re,p.re), (p.im,p.im), (-p.im,-p.im)
+
+// xu: offset-binary bytes [r0 i0 r1 i1].  Returns packed signed bytes of sat8(rint(127 * x*p)).
+//   convert : volk_8i_s32f_convert_32f   -> (float)s8 * float(1/127)            (cdsp.cc:41-44)
+//   rotate  : volk_32fc_s32fc_multiply_32fc, AVX+FMA kernel rounding
+//             re = fma(xr, p.re, -(xi*p.im)), im = fma(xi, p.re, xr*p.im)        (cdsp.cc:46-49)
+//   pack    : volk_32f_s32f_convert_8i   -> sat8(rint(v * 127))                  (cdsp.cc:51-54)
+template <bool CF>
+__device__ __forceinline__ uint32_t rotate_pack_word(uint32_t xu, const RotConst &k, float2 *cf_out) {
+    float2 R = make_float2(__uint_as_float(__byte_perm(xu, 0x4B000000u, 0x7440)),
+                           __uint_as_float(__byte_perm(xu, 0x4B000000u, 0x7442)));
+    float2 I = make_float2(__uint_as_float(__byte_perm(xu, 0x4B000000u, 0x7441)),
+                           __uint_as_float(__byte_perm(xu, 0x4B000000u, 0x7443)));
+    const float2 mk = make_float2(-8388736.0f, -8388736.0f);            // -(2^23 + 128)
+    const float2 c127 = make_float2(0x1.020408p-7f, 0x1.020408p-7f);   // float(1.0/127.0)
+    const float2 s127 = make_float2(127.0f, 127.0f);
+    R = __fmul2_rn(__fadd2_rn(R, mk), c127);
+    I = __fmul2_rn(__fadd2_rn(I, mk), c127);
+    float2 yR = __ffma2_rn(R, k.px, __fmul2_rn(I, k.npy));
+    float2 yI = __ffma2_rn(I, k.px, __fmul2_rn(R, k.py));
+    if (CF) { cf_out[0] = make_float2(yR.x, yI.x); cf_out[1] = make_float2(yR.y, yI.y); }
+    float2 sR = __fmul2_rn(yR, s127), sI = __fmul2_rn(yI, s127);
+    int r0 = __float2int_rn(sR.x), r1 = __float2int_rn(sR.y);           // NaN -> 0
+    int i0 = __float2int_rn(sI.x), i1 = __float2int_rn(sI.y);
+    uint32_t hi, out;
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(i1), "r"(r1), "r"(0));
+    asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(out) : "r"(i0), "r"(r0), "r"(hi));
+    return out;
 }
 
-// rotate two samples (one 32-bit word of signed bytes) by p and pack back to signed bytes
-__device__ __forceinline__ uint32_t rotate_pack_word(uint32_t xs, float2 p, float2 *cf_out) {
-    const uint32_t xu = xs ^ 0x80808080u;
-    float r0 = byte_to_float<0>(xu), i0 = byte_to_float<1>(xu);
-    float r1 = byte_to_float<2>(xu), i1 = byte_to_float<3>(xu);
-    // volk_32fc_s32fc_multiply_32fc, x86 AVX+FMA kernel rounding: fmaddsub(a, re(p), swap(a)*im(p))
-    float yr0 = __fmaf_rn(r0, p.x, -__fmul_rn(i0, p.y)), yi0 = __fmaf_rn(i0, p.x, __fmul_rn(r0, p.y));
-    float yr1 = __fmaf_rn(r1, p.x, -__fmul_rn(i1, p.y)), yi1 = __fmaf_rn(i1, p.x, __fmul_rn(r1, p.y));
-    if (cf_out) { cf_out[0] = make_float2(yr0, yi0); cf_out[1] = make_float2(yr1, yi1); }
-    uint32_t b0 = float_to_s8_bits(yr0), b1 = float_to_s8_bits(yi0);
-    uint32_t b2 = float_to_s8_bits(yr1), b3 = float_to_s8_bits(yi1);
-    uint32_t lo = __byte_perm(b0, b1, 0x0040), hi = __byte_perm(b2, b3, 0x0040);
-    return __byte_perm(lo, hi, 0x5410);
-}
-
+template <bool SIGNED_IN, bool CF>
 __global__ void __launch_bounds__(kApplyThreads)
 k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
     __shared__ uint32_t s_item;
@@ -109,12 +121,14 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
     const uint32_t b = p.block0 + item / (parts * p.nch);
     const uint32_t B = p.B, L = B >> 1;
     const uint32_t part_bytes = B < kPartBytes ? B : kPartBytes;
-    const int nchunk_part = part_bytes >> 4;
+    const int nchunk_part = part_bytes >> 4, nchunks = B >> 4;
     const int chunk0 = part * (kPartBytes >> 4);
     const size_t bc = (size_t)b * p.nch + c;
+    // input bytes -> signed / offset-binary views: one of the two is the raw word
+    constexpr uint32_t kToSigned = SIGNED_IN ? 0u : 0x80808080u;
 
-    const uint8_t *xin = p.iq + bc * B;
-    const uint8_t *rin = p.iq + (size_t)b * p.nch * B;
+    const uint4 *xin = reinterpret_cast<const uint4 *>(p.iq + bc * B);
+    const uint4 *rin = reinterpret_cast<const uint4 *>(p.iq + (size_t)b * p.nch * B);
     const size_t hdr = p.noheader ? 0 : 16 + 4 * (size_t)p.nch;
     int8_t *pkt = p.packets + (size_t)b * p.pitch + p.lead;
     uint4 *col = reinterpret_cast<uint4 *>(pkt + hdr + (size_t)c * B);
@@ -125,17 +139,18 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
         for (int i = 0; i < kChunksPerThread; i++) {
             int jl = tid + i * kApplyThreads;
             if (jl < nchunk_part) {
-                uint4 v = __ldg(reinterpret_cast<const uint4 *>(rin) + chunk0 + jl);
-                v.x ^= p.xormask; v.y ^= p.xormask; v.z ^= p.xormask; v.w ^= p.xormask;
+                uint4 v = __ldg(rin + chunk0 + jl);
+                v.x ^= kToSigned; v.y ^= kToSigned; v.z ^= kToSigned; v.w ^= kToSigned;
                 col[chunk0 + jl] = v;
-                if (p.cf32) {
+                if (CF) {
                     float2 *o = p.cf32 + bc * L + (size_t)(chunk0 + jl) * 8;
                     const uint32_t wv[4] = { v.x, v.y, v.z, v.w };
+                    const float cc = 0x1.020408p-7f;
 #pragma unroll
                     for (int k = 0; k < 4; k++) {
-                        uint32_t xu = wv[k] ^ 0x80808080u;
-                        o[2 * k] = make_float2(byte_to_float<0>(xu), byte_to_float<1>(xu));
-                        o[2 * k + 1] = make_float2(byte_to_float<2>(xu), byte_to_float<3>(xu));
+                        int w = (int)wv[k];
+                        o[2 * k] = make_float2(__fmul_rn((float)(signed char)(w & 0xff), cc), __fmul_rn((float)(signed char)((w >> 8) & 0xff), cc));
+                        o[2 * k + 1] = make_float2(__fmul_rn((float)(signed char)((w >> 16) & 0xff), cc), __fmul_rn((float)(signed char)((w >> 24) & 0xff), cc));
                     }
                 }
             }
@@ -174,17 +189,17 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
     const int sh = p.apply_shift ? lagi : 0;
 
     // ---- load x' (kept in registers) and r, exact integer conjugate dot product ---------------
-    uint4 xv[kChunksPerThread];
+    uint4 xv[kChunksPerThread];                           // signed bytes
     int acc_re = 0, acc_u = 0, acc_v = 0;
 #pragma unroll
     for (int i = 0; i < kChunksPerThread; i++) {
         int jl = tid + i * kApplyThreads;
         uint4 xr = make_uint4(0, 0, 0, 0), rr = make_uint4(0, 0, 0, 0);
         if (jl < nchunk_part) {
-            xr = load_x_chunk(xin, chunk0 + jl, sh, B, p.xormask);
-            rr = __ldg(reinterpret_cast<const uint4 *>(rin) + chunk0 + jl);
-            xr.x ^= p.xormask; xr.y ^= p.xormask; xr.z ^= p.xormask; xr.w ^= p.xormask;
-            rr.x ^= p.xormask; rr.y ^= p.xormask; rr.z ^= p.xormask; rr.w ^= p.xormask;
+            xr = load_x_chunk(xin, chunk0 + jl, sh, nchunks, kToSigned);
+            rr = __ldg(rin + chunk0 + jl);
+            xr.x ^= kToSigned; xr.y ^= kToSigned; xr.z ^= kToSigned; xr.w ^= kToSigned;
+            rr.x ^= kToSigned; rr.y ^= kToSigned; rr.z ^= kToSigned; rr.w ^= kToSigned;
         }
         xv[i] = xr;
         const uint32_t xw[4] = { xr.x, xr.y, xr.z, xr.w }, rw[4] = { rr.x, rr.y, rr.z, rr.w };
@@ -216,15 +231,10 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
             int pre = vre, pim = vu - 2 * vv;                                  // sum xi*rr - xr*ri
             if (parts > 1) {
                 // exchange the partial sums of the sibling parts (tickets are adjacent)
-                if (lane == 0) {
-                    p.partial[bc * parts + part] = make_int2(pre, pim);
-                    __threadfence();
-                    st_release(&p.pflag[bc * parts + part], p.epoch);
-                }
+                if (lane == 0) publish16(&p.partial[bc * parts + part], (uint32_t)pre, (uint32_t)pim, p.epoch);
                 for (uint32_t k = lane; k < parts; k += 32) {
-                    while (ld_acquire(&p.pflag[bc * parts + k]) != p.epoch) __nanosleep(64);
-                    int2 v = __ldcg(&p.partial[bc * parts + k]);
-                    sre += v.x; sim += v.y;
+                    uint4 v = poll16(&p.partial[bc * parts + k], p.epoch);
+                    sre += (int)v.x; sim += (int)v.y;
                 }
 #pragma unroll
                 for (int off = 16; off > 0; off >>= 1) {
@@ -240,11 +250,7 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
             float m = __fsqrt_rn(__fmaf_rn(cr, cr, __fmul_rn(ci, ci)));
             float inv = __fdiv_rn(1.0f, m);
             q = make_float2(__fmul_rn(cr, inv), -__fmul_rn(ci, inv));
-            if (lane == 0 && part == 0) {
-                p.q[bc] = q;
-                __threadfence();
-                st_release(&p.flag[bc], p.epoch);
-            }
+            if (lane == 0 && part == 0) publish16(&p.q[bc], __float_as_uint(q.x), __float_as_uint(q.y), p.epoch);
         }
         // ---- decoupled look-back over earlier blocks of this channel --------------------------
         const int D = p.lookback;
@@ -254,9 +260,8 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
             const bool en = j >= 0 && (p.refnoise ? (p.refnoise[j] != 0) : (p.refnoise_scalar != 0));
             float2 qv = make_float2(0.f, 0.f);
             if (en) {
-                const size_t jc = (size_t)j * p.nch + c;
-                while (ld_acquire(&p.flag[jc]) != p.epoch) __nanosleep(64);
-                qv = __ldcg(&p.q[jc]);
+                uint4 v = poll16(&p.q[(size_t)j * p.nch + c], p.epoch);
+                qv = make_float2(__uint_as_float(v.x), __uint_as_float(v.y));
             }
             const uint32_t m = __ballot_sync(0xffffffffu, en);
             const int pos = cnt + __popc(m & ((1u << lane) - 1u));
@@ -269,6 +274,7 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
             float2 pp; int i;
             if (cnt < D) { pp = p.state_in[c].phasecorrprev; i = cnt - 1; }   // reached batch start: exact
             else { pp = s_q[D - 1]; i = D - 2; }                              // truncated tail
+#pragma unroll 4
             for (; i >= 0; i--) {
                 float2 qq = s_q[i];
                 pp.x = __fadd_rn(__fmul_rn(a, qq.x), __fmul_rn(na, pp.x));    // csdrdevice.cc:67
@@ -294,28 +300,26 @@ k_apply(const ApplyLaunch p, uint32_t ticket0, uint32_t parts) {
     }
     __syncthreads();
     const float2 pc = s_p;
-    const bool pnan = (pc.x != pc.x) || (pc.y != pc.y);
+    RotConst rk;
+    rk.px = make_float2(pc.x, pc.x); rk.py = make_float2(pc.y, pc.y); rk.npy = make_float2(-pc.y, -pc.y);
 
     // ---- rotate (csdrdevice::phasecorrect) and pack (cpacketize::write) ------------------------
 #pragma unroll
     for (int i = 0; i < kChunksPerThread; i++) {
         int jl = tid + i * kApplyThreads;
         if (jl < nchunk_part) {
-            float2 *cf = p.cf32 ? p.cf32 + bc * L + (size_t)(chunk0 + jl) * 8 : nullptr;
+            float2 *cf = CF ? p.cf32 + bc * L + (size_t)(chunk0 + jl) * 8 : nullptr;
             uint4 o;
-            if (pnan) {      // |S| = 0: the reference propagates NaN (csdrdevice.cc:63); bytes become 0
-                o = make_uint4(0, 0, 0, 0);
-                if (cf) for (int k = 0; k < 8; k++) cf[k] = make_float2(pc.x, pc.y);
-            } else {
-                o.x = rotate_pack_word(xv[i].x, pc, cf);
-                o.y = rotate_pack_word(xv[i].y, pc, cf ? cf + 2 : nullptr);
-                o.z = rotate_pack_word(xv[i].z, pc, cf ? cf + 4 : nullptr);
-                o.w = rotate_pack_word(xv[i].w, pc, cf ? cf + 6 : nullptr);
-            }
+            o.x = rotate_pack_word<CF>(xv[i].x ^ 0x80808080u, rk, cf);
+            o.y = rotate_pack_word<CF>(xv[i].y ^ 0x80808080u, rk, cf + 2);
+            o.z = rotate_pack_word<CF>(xv[i].z ^ 0x80808080u, rk, cf + 4);
+            o.w = rotate_pack_word<CF>(xv[i].w ^ 0x80808080u, rk, cf + 6);
             col[chunk0 + jl] = o;
         }
     }
 }
+
+uint32_t apply_parts(uint32_t B) { return B > kPartBytes ? B / kPartBytes : 1; }
 
 cudaError_t launch_apply(const ApplyLaunch &p, cudaStream_t st) {
     const uint32_t parts = apply_parts(p.B);
@@ -323,10 +327,12 @@ cudaError_t launch_apply(const ApplyLaunch &p, cudaStream_t st) {
     if (n_items == 0) return cudaSuccess;
     if (p.lookback < 1 || p.lookback > kMaxLookback) return cudaErrorInvalidValue;
     const size_t smem = (size_t)(p.lookback + 32) * sizeof(float2);
-    k_apply<<<n_items, kApplyThreads, smem, st>>>(p, p.ticket0, parts);
+    const bool sgn = p.xormask == 0, cf = p.cf32 != nullptr;
+    if (sgn && cf)       k_apply<true, true><<<n_items, kApplyThreads, smem, st>>>(p, p.ticket0, parts);
+    else if (sgn)        k_apply<true, false><<<n_items, kApplyThreads, smem, st>>>(p, p.ticket0, parts);
+    else if (cf)         k_apply<false, true><<<n_items, kApplyThreads, smem, st>>>(p, p.ticket0, parts);
+    else                 k_apply<false, false><<<n_items, kApplyThreads, smem, st>>>(p, p.ticket0, parts);
     return cudaGetLastError();
 }
-
-uint32_t apply_parts(uint32_t B) { return B > kPartBytes ? B / kPartBytes : 1; }
 
 }  // namespace coh

@@ -43,7 +43,7 @@ struct ApplyLaunch {
     float *lag, *mag; float2 *phase; uint8_t *measured;      // per (block, channel) outputs
     float2 *cf32;                                            // optional corrected float matrix
     // look-back scratch
-    float2 *q; uint32_t *flag; int2 *partial; uint32_t *pflag; uint32_t epoch;
+    uint4 *q; uint4 *partial; uint32_t epoch;   // 16-byte records {a, b, epoch, check}
     uint32_t *ticket; uint32_t ticket0;     // device counter and its value at launch
     int sm_count;
 };
