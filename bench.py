@@ -55,6 +55,11 @@ class ClockSampler:
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            # NVML start-up takes driver locks for a while on an 8-GPU box: do not let it
+            # overlap the timed region -- wait for the first sample before returning
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 15.0 and self.proc.poll() is None:
+                time.sleep(0.05)
         except Exception:
             self.proc = None
 

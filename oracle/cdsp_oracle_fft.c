@@ -12,7 +12,7 @@
 #include <string.h>
 #include <pthread.h>
 
-#define ORC_MAX_PLANS 8
+#define ORC_MAX_PLANS 64
 typedef struct { int n; orc_cf32 *tw; } orc_plan;
 static orc_plan g_plans[ORC_MAX_PLANS];
 static int g_nplans = 0;

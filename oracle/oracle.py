@@ -150,3 +150,97 @@ def np_pack8(v):
     r = (v.astype(np.float32) * np.float32(127.0))
     r = np.clip(r, np.float32(-128.0), np.float32(127.0))
     return np.rint(r).astype(np.int8)
+
+
+# ------------------------------------------------- the reference's own TUs (oracle/_ref) -----
+# libref_cdsp.so = /root/reference's cdsp.cc, ccoherent.cc, csdrdevice.cc, crtlsdr.cc,
+# cpacketizer.cc, common.cc, ccontrol.cc compiled unmodified against oracle/shim/ plus
+# oracle/ref_harness.cc.  Built in the build container only; the GPU box uses the prebuilt file.
+
+_ref = None
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_LIB_PATH)
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        if not ref_available():
+            raise RuntimeError(f"{REF_LIB_PATH} is not built (needs /root/reference: make -C oracle ref)")
+        L = C.CDLL(REF_LIB_PATH)
+        vp, u32, i = C.c_void_p, C.c_uint32, C.c_int
+        L.refh_create.restype = vp
+        L.refh_create.argtypes = [u32, u32, i, i]
+        L.refh_destroy.argtypes = [vp]
+        L.refh_packet_len.restype = C.c_size_t
+        L.refh_packet_len.argtypes = [vp]
+        L.refh_sent_len.restype = C.c_size_t
+        L.refh_sent_len.argtypes = [vp]
+        L.refh_run_batch.argtypes = [vp, vp, u32, vp, i, vp, vp, vp, vp, vp, vp]
+        L.refh_get_state.argtypes = [vp, vp, vp]
+        L.refh_cdsp_convtosigned.argtypes = [vp, vp, i]
+        L.refh_cdsp_convtofloat.argtypes = [vp, vp, i]
+        L.refh_cdsp_convto8bit.argtypes = [vp, vp, i]
+        L.refh_cdsp_scalarmul.argtypes = [vp, vp, C.c_float, C.c_float, i]
+        L.refh_cdsp_conj_dotproduct.argtypes = [vp, vp, vp, i]
+        L.refh_cdsp_rms.argtypes = [vp, i]
+        L.refh_cdsp_rms.restype = C.c_float
+        L.refh_cdsp_crestfactor.argtypes = [vp, i]
+        L.refh_cdsp_crestfactor.restype = C.c_float
+        L.refh_cdsp_magsquared.argtypes = [vp, vp, i]
+        L.refh_cdsp_conjugatemul.argtypes = [vp, vp, vp, i]
+        L.refh_cdsp_indexofmax.argtypes = [vp, i]
+        L.refh_cdsp_indexofmax.restype = C.c_uint32
+        _ref = L
+    return _ref
+
+
+class RefCdsp:
+    """The reference's own ccoherent/csdrdevice/cpacketize objects, fed block by block
+    (oracle/ref_harness.cc).  One live instance per process (cpacketize is all-static).
+    nfft=8 is the reference's compile-time value (src/main.cc:165): at most 7 lags per block."""
+
+    def __init__(self, n_signal, blocksize, noheader=False, nfft=8):
+        self.lib = ref_lib()
+        self.h = self.lib.refh_create(n_signal, blocksize, int(noheader), nfft)
+        if not self.h:
+            raise RuntimeError("refh_create failed (another instance live, or bad geometry)")
+        self.nch, self.B = n_signal + 1, blocksize
+        self.packet_len = self.lib.refh_packet_len(self.h)
+        self.sent_len = self.lib.refh_sent_len(self.h)
+
+    def run_batch(self, iq, lag_request=None, lag_mode=1, refnoise=None):
+        iq = np.ascontiguousarray(iq, dtype=np.uint8)
+        nb = iq.shape[0]
+        assert iq.shape[1:] == (self.nch, self.B)
+        out = {"packets": np.zeros((nb, self.packet_len), dtype=np.int8),
+               "lag": np.zeros((nb, self.nch), dtype=np.float32),
+               "mag": np.zeros((nb, self.nch), dtype=np.float32),
+               "phase": np.zeros((nb, self.nch), dtype=np.complex64),
+               "measured": np.zeros((nb, self.nch), dtype=np.uint8)}
+        lr = None if lag_request is None else np.ascontiguousarray(lag_request, dtype=np.uint8)
+        rn = None if refnoise is None else np.ascontiguousarray(refnoise, dtype=np.uint8)
+        rc = self.lib.refh_run_batch(self.h, _p(iq), nb, _p(lr), int(lag_mode), _p(rn), _p(out["packets"]),
+                                     _p(out["lag"]), _p(out["mag"]), _p(out["phase"]), _p(out["measured"]))
+        if rc:
+            raise RuntimeError(f"refh_run_batch failed ({rc})")
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.refh_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -65,3 +65,103 @@ def test_track_mode_matches_oracle(pkg, synth, oracle, B, C, nb):
         err = np.angle(np.exp(1j * (est - info["phases"])))
         assert np.abs(err).max() < 5e-3 * max(1.0, (8192 / (B // 2)) ** 0.5)
     eng.close()
+
+
+# ---- against the reference's own output (tests/golden/*.npz, from oracle/_ref) ----------------
+import glob
+import os
+
+_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+_CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(_GOLD, "*.npz")))
+
+
+@pytest.mark.parametrize("name", _CASES)
+def test_cuda_path_matches_reference_golden(pkg, name):
+    """Reference configuration (no software shift, nfft-1 = 7 lag slots) on the reference's own
+    inputs: integer lag bit-exact, phase within 1e-4 rad, packets within 1e-4 relative L2
+    (BASELINE.json north_star tolerances); header, readcnt and the ref column byte-exact."""
+    d = np.load(os.path.join(_GOLD, name + ".npz"))
+    C, B, nb, noheader, nfft, _ = (int(x) for x in d["meta"])
+    eng = pkg.CoherentCuda(C, B, noheader=bool(noheader), apply_shift=False, max_lag_slots=nfft - 1)
+    out = eng.batch(d["iq"], lag_request=d["lag_request"], refnoise=d["refnoise"], readcnt0=8)
+    np.testing.assert_array_equal(out["lag"], d["lag"])
+    np.testing.assert_allclose(out["mag"], d["mag"], rtol=1e-4)
+    assert np.abs(np.angle(out["phase"] * np.conj(d["phase"]))).max() < 1e-4
+    np.testing.assert_allclose(np.abs(out["phase"]), np.abs(d["phase"]), atol=1e-5)
+    hdr = eng.hdr_len
+    np.testing.assert_array_equal(out["packets"][:, :hdr + B], d["packets"][:, :hdr + B])
+    assert _rel_l2(out["packets"][:, hdr:], d["packets"][:, hdr:]) < 1e-4
+    assert (out["packets"] != d["packets"]).mean() < 1e-3          # isolated +-1 LSB rounding flips only
+    assert np.abs(out["packets"].astype(int) - d["packets"].astype(int)).max() <= 1
+    eng.close()
+
+
+def test_streaming_block_calls_match_batch(pkg, synth):
+    """cohcuda_submit_block / wait_block (the per-block call ccoherent::threadf makes) give the
+    same bytes as one cohcuda_batch over the same blocks, state carried across calls."""
+    C, B, nb = 3, 4096, 9
+    iq, _ = synth.make_blocks(C, B, nb, seed=77, delays=np.array([3, -20, 64]))
+    req = np.zeros((nb, C + 1), np.uint8); req[0, 1:] = 1; req[5, 2] = 1
+    a = pkg.CoherentCuda(C, B, apply_shift=True)
+    whole = a.batch(iq, lag_request=req, readcnt0=0)
+    a.close()
+    s = pkg.CoherentCuda(C, B, apply_shift=True)
+    for b in range(nb):
+        s.submit_block([iq[b, c] for c in range(C + 1)], readcnt=np.full(C + 1, b, np.uint32), lag_request=req[b])
+        r = s.wait_block()
+        np.testing.assert_array_equal(r["packet"], whole["packets"][b])
+        np.testing.assert_array_equal(r["lag"], whole["lag"][b])
+        np.testing.assert_array_equal(r["phase"].view(np.uint32), whole["phase"][b].view(np.uint32))
+        assert r["globalseqn"] == b and (r["measured"][1:] == req[b, 1:]).all()
+    st = s.get_state()
+    assert [st[c].held_lag for c in range(1, C + 1)] == [3, -20, 64]
+    s.close()
+
+
+def test_cdsp_primitives_match_oracle(pkg, oracle):
+    """The ten cdsp:: statics as single kernels through the C ABI (include/cdsp.h:36-71)."""
+    import ctypes as C_
+    eng = pkg.CoherentCuda(1, 64)
+    L, lib, h = oracle.lib(), eng.lib, eng.h
+    rng = np.random.default_rng(5)
+    p = lambda a: a.ctypes.data
+    u8 = rng.integers(0, 256, 8192, dtype=np.uint8); s8g = np.empty_like(u8); s8o = np.empty_like(u8)
+    assert lib.cohcuda_cdsp_convtosigned(h, p(u8), p(s8g), 8192) == 0
+    L.orc_convtosigned(p(u8), p(s8o), 8192); np.testing.assert_array_equal(s8g, s8o)
+    fg, fo = np.empty(8192, np.float32), np.empty(8192, np.float32)
+    assert lib.cohcuda_cdsp_convtofloat(h, p(fg), p(s8g), 8192) == 0
+    L.orc_convtofloat(p(fo), p(s8o), 8192); np.testing.assert_array_equal(fg.view(np.uint32), fo.view(np.uint32))
+    x = (rng.standard_normal(8192) * 0.7).astype(np.float32)
+    qg, qo = np.empty(8192, np.int8), np.empty(8192, np.int8)
+    assert lib.cohcuda_cdsp_convto8bit(h, p(qg), p(x), 4096) == 0
+    L.orc_convto8bit(p(qo), p(x), 8192); np.testing.assert_array_equal(qg, qo)
+    z = (rng.standard_normal(4096) + 1j * rng.standard_normal(4096)).astype(np.complex64)
+    w = (rng.standard_normal(4096) + 1j * rng.standard_normal(4096)).astype(np.complex64)
+    og, oo = np.empty_like(z), np.empty_like(z)
+    assert lib.cohcuda_cdsp_scalarmul(h, p(og), p(z), C_.c_float(0.6), C_.c_float(-0.8), 4096) == 0
+    L.orc_scalarmul(p(oo), p(z), oracle.Cf32(0.6, -0.8), 4096)
+    np.testing.assert_array_equal(og.view(np.uint32), oo.view(np.uint32))
+    assert lib.cohcuda_cdsp_conjugatemul(h, p(og), p(z), p(w), 4096) == 0
+    L.orc_conjugatemul(p(oo), p(z), p(w), 4096)
+    np.testing.assert_allclose(og, oo, rtol=1e-6, atol=1e-6)
+    mg, mo = np.empty(4096, np.float32), np.empty(4096, np.float32)
+    assert lib.cohcuda_cdsp_magsquared(h, p(mg), p(z), 4096) == 0
+    L.orc_magsquared(p(mo), p(z), 4096); np.testing.assert_allclose(mg, mo, rtol=1e-6)
+    mo[100] = mo[700] = mo.max() + 1
+    idx = np.zeros(1, np.uint32)
+    assert lib.cohcuda_cdsp_indexofmax(h, p(idx), p(mo), 4096) == 0 and idx[0] == 100
+    res = np.empty(2, np.float32)
+    assert lib.cohcuda_cdsp_conj_dotproduct(h, p(res), p(z), p(w), 4096) == 0
+    want = np.vdot(w.astype(np.complex128), z.astype(np.complex128))      # sum z * conj(w)
+    assert abs(complex(res[0], res[1]) - want) / abs(want) < 1e-5
+    r = np.empty(1, np.float32)
+    assert lib.cohcuda_cdsp_rms(h, p(r), p(x), 8192) == 0
+    assert abs(r[0] - np.sqrt((x.astype(np.float64) ** 2).mean())) < 1e-5
+    for n in (32, 256, 16384):
+        xi = (rng.standard_normal((3, n)) + 1j * rng.standard_normal((3, n))).astype(np.complex64)
+        for sign in (-1, 1):
+            yo = np.empty_like(xi)
+            assert lib.cohcuda_cdsp_fft(h, p(yo), p(xi), n, 3, sign) == 0
+            want = np.fft.fft(xi.astype(np.complex128), axis=1) if sign < 0 else np.fft.ifft(xi.astype(np.complex128), axis=1) * n
+            assert np.linalg.norm(yo - want) / np.linalg.norm(want) < 2e-6
+    eng.close()
