@@ -164,8 +164,10 @@ class CoherentCuda:
         self._check(self.lib.cohcuda_sync(self.h), "cohcuda_sync")
 
     def batch(self, iq, lag_mode=LAG_ALL, lag_request=None, refnoise=None, refnoise_enabled=True,
-              input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0):
-        """Host-array convenience: iq uint8 [n_blocks][C+1][B] -> dict of numpy outputs."""
+              input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0, cf32_dev=None):
+        """Host-array convenience: iq uint8 [n_blocks][C+1][B] -> dict of numpy outputs.
+        cf32_dev: optional DEVICE pointer (int) receiving the corrected float matrix
+        [n_blocks][C+1][L] complex64."""
         iq = np.ascontiguousarray(iq, dtype=np.uint8)
         nb = iq.shape[0]
         assert iq.shape[1:] == (self.nch, self.B), iq.shape
@@ -182,7 +184,7 @@ class CoherentCuda:
                        refnoise=rn, refnoise_enabled=int(refnoise_enabled),
                        input_is_signed=int(input_is_signed), readcnt=rc_, readcnt0=readcnt0,
                        globalseqn0=globalseqn0, packets=out["packets"], packets_on_device=0,
-                       lag=out["lag"], mag=out["mag"], phasecorr=out["phase"])
+                       lag=out["lag"], mag=out["mag"], phasecorr=out["phase"], cf32=cf32_dev)
         self.sync()
         return out
 
