@@ -189,7 +189,7 @@ def run_gpu_arm(args):
     stream = torch.cuda.Stream(device=dev)
     nb, nch, B, L = args.blocks, C_SIG + 1, BLOCKSIZE, BLOCKSIZE // 2
     eng = pkg.CoherentCuda(C_SIG, B, apply_shift=True, device=local, max_batch_blocks=nb,
-                           stream=stream.cuda_stream)
+                           stream=stream.cuda_stream, alpha=args.alpha)
     # each rank holds its own shard of blocks and its own copy of the reference channel
     iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev)
     pk_dev = torch.zeros(nb * eng.dev_pitch + 16, dtype=torch.int8, device=dev)
@@ -211,7 +211,8 @@ def run_gpu_arm(args):
 
     def step_dev(mode):
         eng.batch_raw(iq=iq.data_ptr(), iq_on_device=1, n_blocks=nb,
-                      lag_mode=pkg.LAG_ALL if mode == "sync" else pkg.LAG_NONE, refnoise_enabled=1,
+                      lag_mode=pkg.LAG_ALL if mode == "sync" else pkg.LAG_NONE,
+                      refnoise_enabled=0 if args.no_refnoise else 1,
                       packets=pk_dev.data_ptr(), packets_on_device=1)
 
     def timed(fn, steps, warmup):
@@ -358,6 +359,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--cpu-blocks", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--alpha", type=float, default=0.5, help="phase IIR weight (reference: 0.5)")
+    ap.add_argument("--no-refnoise", action="store_true", help="diagnostic: noise source off (no phase estimate)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
