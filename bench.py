@@ -31,6 +31,16 @@ BYTES_PER_SAMPLE = 4.0            # 2 B u8 IQ in + 2 B int8 IQ out (p
 FLOP_PER_SAMPLE_SYNC = 311.0      # SURVEY 8d algorithmic flops per coherent sample, SYNC mode
 
 
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)[kernel]
+        return t["bytes_per_launch"], t["source"]
+    except Exception:
+        return None, None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -259,8 +269,9 @@ def run_gpu_arm(args):
             k = prof["track"]["k_apply"]; units = 2 * nch * nb * L
             name = "k_apply"
         gbs = units * BYTES_PER_SAMPLE / (k["ms"] * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(name) if nb == N_BLOCKS else (None, None)
         r = {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-             "frac": gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+             "frac": gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
              "launches_timed": k["launches"], "avg_launch_ms": k["ms"] / max(k["launches"], 1),
              "algorithmic_bytes_per_launch": units * BYTES_PER_SAMPLE / max(k["launches"], 1)}
         if mode == "sync":

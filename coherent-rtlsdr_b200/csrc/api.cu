@@ -5,6 +5,7 @@
 #include "kernels.h"
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -51,6 +52,7 @@ struct cohcuda {
 };
 
 static constexpr uint32_t kCorrChunk = 148;             // blocks per K1/K2 launch: items = 148*C
+static constexpr uint32_t kPipeChunk = 74;              // same, when host copies are pipelined around the kernels
 
 #define CK(call)                                                                        \
     do {                                                                                \

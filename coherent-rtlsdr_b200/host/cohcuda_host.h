@@ -1,0 +1,22 @@
+/* host/cohcuda_host.h -- helpers shared by the drop-in translation units (host/cdsp.cc,
+ * host/ccoherent.cc) that replace the reference's src/cdsp.cc and src/ccoherent.cc.
+ * The class declarations those files implement are the reference's own headers
+ * (include/cdsp.h, include/ccoherent.h), unchanged. */
+#ifndef COHCUDA_HOST_H
+#define COHCUDA_HOST_H
+#include "coherent_cuda.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+/* process-wide handle used by the cdsp:: statics (device from $COHCUDA_DEVICE, default 0) */
+cohcuda_t *cohcuda_host_prim_handle(void);
+/* replacement for fftwf_plan_many_dft(1, {n}, howmany, in, .., 1, n, out, .., 1, n, sign, 0)
+ * (src/ccoherent.cc:87-93): the object an fft_scheme must point to for cdsp::fft on this path */
+void *cohcuda_host_make_fft_scheme(int n, int howmany, int sign, void *in, void *out);
+void cohcuda_host_destroy_fft_scheme(void *scheme);
+/* the engine a ccoherent instance drives (NULL if none is alive); for status displays/tests */
+cohcuda_t *cohcuda_host_engine(const void *ccoherent_instance);
+#ifdef __cplusplus
+}
+#endif
+#endif

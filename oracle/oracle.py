@@ -157,19 +157,28 @@ def np_pack8(v):
 # cpacketizer.cc, common.cc, ccontrol.cc compiled unmodified against oracle/shim/ plus
 # oracle/ref_harness.cc.  Built in the build container only; the GPU box uses the prebuilt file.
 
-_ref = None
+# libdropin_cuda.so = the same harness and reference TUs, except that src/cdsp.cc and
+# src/ccoherent.cc are replaced by the product's host/cdsp.cc and host/ccoherent.cc over
+# libcoherent_cuda.so (needs a GPU at run time; tests/test_dropin.py).
+DROPIN_LIB_PATH = os.path.join(HERE, "_ref", "libdropin_cuda.so")
+
+_ref = {}
 
 
 def ref_available() -> bool:
     return os.path.exists(REF_LIB_PATH)
 
 
-def ref_lib():
-    global _ref
-    if _ref is None:
-        if not ref_available():
-            raise RuntimeError(f"{REF_LIB_PATH} is not built (needs /root/reference: make -C oracle ref)")
-        L = C.CDLL(REF_LIB_PATH)
+def dropin_available() -> bool:
+    return os.path.exists(DROPIN_LIB_PATH)
+
+
+def ref_lib(path=None):
+    path = path or REF_LIB_PATH
+    if path not in _ref:
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} is not built (needs /root/reference: make -C oracle ref dropin)")
+        L = C.CDLL(path)
         vp, u32, i = C.c_void_p, C.c_uint32, C.c_int
         L.refh_create.restype = vp
         L.refh_create.argtypes = [u32, u32, i, i]
@@ -193,8 +202,8 @@ def ref_lib():
         L.refh_cdsp_conjugatemul.argtypes = [vp, vp, vp, i]
         L.refh_cdsp_indexofmax.argtypes = [vp, i]
         L.refh_cdsp_indexofmax.restype = C.c_uint32
-        _ref = L
-    return _ref
+        _ref[path] = L
+    return _ref[path]
 
 
 class RefCdsp:
@@ -202,8 +211,8 @@ class RefCdsp:
     (oracle/ref_harness.cc).  One live instance per process (cpacketize is all-static).
     nfft=8 is the reference's compile-time value (src/main.cc:165): at most 7 lags per block."""
 
-    def __init__(self, n_signal, blocksize, noheader=False, nfft=8):
-        self.lib = ref_lib()
+    def __init__(self, n_signal, blocksize, noheader=False, nfft=8, lib_path=None):
+        self.lib = ref_lib(lib_path)
         self.h = self.lib.refh_create(n_signal, blocksize, int(noheader), nfft)
         if not self.h:
             raise RuntimeError("refh_create failed (another instance live, or bad geometry)")

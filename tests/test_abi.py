@@ -90,3 +90,15 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
                 assert "cdsp_oracle" not in txt and "orc_" not in txt, f
+
+
+def test_dropin_library_exports_harness_symbols(oracle):
+    """oracle/_ref/libdropin_cuda.so (reference TUs + host/cdsp.cc + host/ccoherent.cc) loads
+    without a GPU and resolves libcoherent_cuda.so through its rpath; no compute call is made."""
+    import ctypes
+    if not oracle.dropin_available():
+        pytest.skip("libdropin_cuda.so not built (needs /root/reference at build time)")
+    L = ctypes.CDLL(oracle.DROPIN_LIB_PATH)
+    for s in ("refh_create", "refh_run_batch", "refh_destroy", "cohcuda_host_prim_handle",
+              "cohcuda_host_make_fft_scheme", "cohcuda_host_engine"):
+        assert hasattr(L, s), s
