@@ -182,6 +182,24 @@ def run_reference_arm(args):
     return 0
 
 
+def bind_to_gpu_numa_node(index):
+    """Run this rank on the CPU cores next to its GPU (NVML's ideal affinity) so that the pinned
+    host buffers of the e2e path are first-touched on that NUMA node; harmless if unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [i for i in range(ncpu) if (words[i // 64] >> (i % 64)) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 # ------------------------------------------------------------------------------------ GPU arm
 def run_gpu_arm(args):
     import torch
@@ -194,6 +212,7 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bind_to_gpu_numa_node(local)
     import cohpkg
     pkg = cohpkg.load()
     stream = torch.cuda.Stream(device=dev)
