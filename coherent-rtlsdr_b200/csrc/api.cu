@@ -24,7 +24,9 @@ struct cohcuda {
     std::string err;
     uint64_t launches = 0;
 
-    float2 *d_TN = nullptr;
+    float2 *d_TN = nullptr, *d_TN_sub = nullptr;   // W_N^n (n < L) and, for L > 8192, W_16384^n (n < 8192)
+    float4 *d_scratch = nullptr;                   // L > 8192: [corr_chunk * C][L] packed elements (fft_big.cu)
+    uint32_t corr_chunk = 0;                       // blocks per K1/K2 launch group
     ChanState *d_state[2] = { nullptr, nullptr };
     int cur = 0;
     uint32_t *d_ticket = nullptr; uint32_t ticket_total = 0, epoch = 0;
@@ -71,7 +73,7 @@ template <typename T> static cudaError_t dalloc(T **p, size_t n) {
 template <typename T> static void dfree(T *&p) { if (p) cudaFree(p); p = nullptr; }
 
 static void free_batch_buffers(cohcuda *h) {
-    dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_refspec); dfree(h->d_peaks);
+    dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_refspec); dfree(h->d_peaks); dfree(h->d_scratch);
     dfree(h->d_lag); dfree(h->d_mag); dfree(h->d_phase); dfree(h->d_meas);
     dfree(h->d_q); dfree(h->d_partial);
     dfree(h->d_src); dfree(h->d_items); dfree(h->d_reflist); dfree(h->d_slot);
@@ -86,8 +88,11 @@ static int ensure_capacity(cohcuda *h, uint32_t nb) {
     const size_t n = (size_t)nb * h->nch, parts = apply_parts(h->B);
     CK(dalloc(&h->d_iq, n * h->B));
     CK(dalloc(&h->d_packets, (size_t)nb * h->pitch + 16));
-    if (correlate_supported(h->B))
-        CK(dalloc(&h->d_refspec, (size_t)kCorrChunk * 2 * h->L));
+    if (correlate_supported(h->B)) {
+        const uint32_t cc = h->corr_chunk < nb ? h->corr_chunk : nb;       // no more slots than blocks
+        CK(dalloc(&h->d_refspec, (size_t)cc * 2 * h->L));
+        if (correlate_is_big(h->B)) CK(dalloc(&h->d_scratch, (size_t)cc * h->cfg.n_signal * h->L));
+    }
     CK(dalloc(&h->d_peaks, n));
     CK(dalloc(&h->d_lag, n)); CK(dalloc(&h->d_mag, n)); CK(dalloc(&h->d_phase, n)); CK(dalloc(&h->d_meas, n));
     CK(dalloc(&h->d_q, n)); CK(dalloc(&h->d_partial, n * parts));
@@ -156,6 +161,19 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
         if ((e = cudaMalloc((void **)&h->d_TN, sizeof(float2) * h->L)) != cudaSuccess) return fail("cudaMalloc", e);
         if ((e = cudaMemcpy(h->d_TN, tn.data(), sizeof(float2) * h->L, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
     }
+    h->corr_chunk = kCorrChunk;
+    if (correlate_supported(B) && correlate_is_big(B)) {
+        // the split path keeps 16 L bytes of scratch per item in flight: bound it to ~256 items
+        uint32_t cc = 256 / cfg->n_signal;
+        h->corr_chunk = cc < 1 ? 1 : (cc > kCorrChunk ? kCorrChunk : cc);
+        std::vector<float2> ts(8192);
+        for (uint32_t n = 0; n < 8192; n++) {
+            double a = -2.0 * M_PI * (double)n / 16384.0;
+            ts[n] = make_float2((float)std::cos(a), (float)std::sin(a));
+        }
+        if ((e = cudaMalloc((void **)&h->d_TN_sub, sizeof(float2) * 8192)) != cudaSuccess) return fail("cudaMalloc", e);
+        if ((e = cudaMemcpy(h->d_TN_sub, ts.data(), sizeof(float2) * 8192, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
+    }
     for (int i = 0; i < 2; i++)
         if ((e = dalloc(&h->d_state[i], (size_t)h->nch)) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = dalloc(&h->d_ticket, (size_t)1)) != cudaSuccess) return fail("cudaMalloc", e);
@@ -189,7 +207,7 @@ extern "C" void cohcuda_destroy(cohcuda_t *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void *p : h->registered) cudaHostUnregister(p);
     free_batch_buffers(h);
-    dfree(h->d_TN); dfree(h->d_state[0]); dfree(h->d_state[1]); dfree(h->d_ticket);
+    dfree(h->d_TN); dfree(h->d_TN_sub); dfree(h->d_state[0]); dfree(h->d_state[1]); dfree(h->d_ticket);
     if (h->h_flags) cudaFreeHost(h->h_flags);
     if (h->h_readcnt) cudaFreeHost(h->h_readcnt);
     if (h->h_lag) cudaFreeHost(h->h_lag);

@@ -20,145 +20,9 @@
 // Forward passes are decimation-in-frequency (natural in, digit-reversed out), inverse passes
 // decimation-in-time (digit-reversed in, natural out), so no reordering pass exists and the
 // reference spectrum is stored in the same digit-reversed order.
-#include "fft_dev.cuh"
-#include "fft_packed.cuh"
-#include "kernels.h"
+#include "fft_passes.cuh"
 
 namespace coh {
-
-constexpr int kFftThreads = 512;
-
-template <int LOG2L> struct Plan {
-    static constexpr int L = 1 << LOG2L;
-    static constexpr int S1 = L / 16;                       // stride of pass 1 (radix 16)
-    static constexpr int M1 = L / 16;                       // sub-transform length after pass 1
-    static constexpr int RA = (M1 / 2 >= 16) ? 16 : (M1 / 2);   // mid pass A radix (1 = none)
-    static constexpr int SA = (RA > 1) ? M1 / RA : M1;
-    static constexpr int RB = (RA > 1 && SA > 2) ? SA / 2 : 1;  // mid pass B radix, stride 2
-    static constexpr int LP = ppadded_len(L);
-    static constexpr size_t kSmemBytes = (size_t)LP * sizeof(float4);
-};
-
-__device__ __forceinline__ float2 load_sample(const uint8_t *x, int n, uint32_t xormask) {
-    // cdsp::convtosigned (src/cdsp.cc:21-34) + volk_8i_s32f_convert_32f (src/cdsp.cc:41-44)
-    unsigned short raw = reinterpret_cast<const unsigned short *>(x)[n];
-    raw ^= (unsigned short)xormask;
-    const float c = 0x1.020408p-7f;                 // float(1.0/127.0)
-    float re = (float)(signed char)(raw & 0xff) * c;
-    float im = (float)(signed char)(raw >> 8) * c;
-    return make_float2(re, im);
-}
-
-// Twiddles of one butterfly, two-level so that few registers stay live: w^(4a+b) = w^(4a) * w^b.
-// Scalar form (the same twiddle for both halves) ...
-struct TwScalar {
-    float2 lo[4], hi[4];                            // w^0..w^3, w^0, w^4, w^8, w^12
-    __device__ __forceinline__ explicit TwScalar(float2 w) {
-        lo[0] = hi[0] = make_float2(1.0f, 0.0f);
-        lo[1] = w; lo[2] = cmul(w, w); lo[3] = cmul(lo[2], w);
-        hi[1] = cmul(lo[2], lo[2]); hi[2] = cmul(hi[1], hi[1]); hi[3] = cmul(hi[2], hi[1]);
-    }
-    __device__ __forceinline__ PC apply(PC v, int k) const {
-        if (k == 0) return v;
-        if (k < 4) return pc_mul(v, lo[k]);
-        if ((k & 3) == 0) return pc_mul(v, hi[k >> 2]);
-        return pc_mul(v, cmul(hi[k >> 2], lo[k & 3]));
-    }
-};
-// ... and packed form: lane A gets w^k, lane B gets g * w^k (the odd-bin modulation rides along)
-struct TwPair {
-    PC lo[4]; float2 hi[4];
-    __device__ __forceinline__ TwPair(float2 w, float2 g) {
-        const float2 w2 = cmul(w, w), w3 = cmul(w2, w);
-        lo[0].r = make_float2(1.0f, g.x); lo[0].i = make_float2(0.0f, g.y);
-        lo[1] = pc_mul(lo[0], w); lo[2] = pc_mul(lo[0], w2); lo[3] = pc_mul(lo[0], w3);
-        hi[0] = make_float2(1.0f, 0.0f);
-        hi[1] = cmul(w2, w2); hi[2] = cmul(hi[1], hi[1]); hi[3] = cmul(hi[2], hi[1]);
-    }
-    __device__ __forceinline__ PC apply(PC v, int k) const {
-        if (k < 4) return pc_mulp(v, lo[k]);
-        return pc_mulp(v, pc_mul(lo[k & 3], hi[k >> 2]));
-    }
-};
-
-// ---- pass 1: global bytes -> shared, radix 16 at stride L/16, both halves ------------------
-template <int LOG2L, bool NEG_B>
-__device__ __forceinline__ void pass1_from_global(const uint8_t *x, uint32_t xormask, float4 *s,
-                                                  const float2 *__restrict__ TN) {
-    using P = Plan<LOG2L>;
-    constexpr int S = P::S1;
-    for (int low = threadIdx.x; low < S; low += kFftThreads) {
-        PC v[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            const float2 a = load_sample(x, low + k * S, xormask);
-            const float2 b = mul_w32<-1>(a, k);       // W_N^(k*L/16) = W_32^k
-            v[k].r = make_float2(a.x, b.x); v[k].i = make_float2(a.y, b.y);
-        }
-        PDft<16, -1>::run(v);
-        float2 g = __ldg(&TN[low]);                   // W_N^low (odd-bin modulation)
-        if (NEG_B) g = make_float2(-g.x, -g.y);       // ref sits in [L,2L): odd bins change sign
-        const TwPair tw(__ldg(&TN[2 * low]), g);      // W_L^low
-#pragma unroll
-        for (int k = 0; k < 16; k++) s[ppad(low + k * S)] = pc_to(tw.apply(v[k], k));
-    }
-}
-
-// ---- in-place mid passes ----------------------------------------------------------------------
-template <int LOG2L, int R, int S, int DIR>
-__device__ __forceinline__ void mid_pass(float4 *s, const float2 *__restrict__ TN) {
-    using P = Plan<LOG2L>;
-    constexpr int NB = P::L / R;                      // butterflies
-    constexpr int TSTEP = 2 * (P::L / (S * R));       // index step into TN for W_(S*R)
-    for (int bf = threadIdx.x; bf < NB; bf += kFftThreads) {
-        const int low = bf & (S - 1), high = bf / S;
-        const int base = high * S * R + low;
-        float2 w = __ldg(&TN[low * TSTEP]);
-        if (DIR > 0) w = cconj(w);
-        const TwScalar tw(w);
-        PC v[R];
-#pragma unroll
-        for (int k = 0; k < R; k++) v[k] = pc_from(s[ppad(base + k * S)]);
-        if (DIR > 0) {
-#pragma unroll
-            for (int k = 1; k < R; k++) v[k] = tw.apply(v[k], k);
-        }
-        PDft<R, DIR>::run(v);
-        if (DIR < 0) {
-#pragma unroll
-            for (int k = 1; k < R; k++) v[k] = tw.apply(v[k], k);
-        }
-#pragma unroll
-        for (int k = 0; k < R; k++) s[ppad(base + k * S)] = pc_to(v[k]);
-    }
-}
-
-// After pass 1 the data is 16 independent sub-transforms of L/16 points; for L = 8192 with 512
-// threads each of them (512 elements) is worked on by exactly one warp in every mid pass and
-// in the pair stage (butterfly bf = thread index), so those passes need only warp-level
-// synchronisation.  The 16 warps then drift apart and one warp's LDS/STS bursts overlap
-// another's arithmetic instead of all warps meeting at a block barrier seven times per item.
-template <int LOG2L> struct WarpLocal { static constexpr bool value = (LOG2L == 13) && (kFftThreads == 512); };
-template <int LOG2L> __device__ __forceinline__ void mid_sync() {
-    if constexpr (WarpLocal<LOG2L>::value) __syncwarp(); else __syncthreads();
-}
-// pair index handled by this thread in trip j of the pair stage
-template <int LOG2L> __device__ __forceinline__ int pair_index(int j) {
-    if constexpr (WarpLocal<LOG2L>::value) return (threadIdx.x >> 5) * 256 + (threadIdx.x & 31) + 32 * j;
-    else return threadIdx.x + kFftThreads * j;
-}
-
-template <int LOG2L, int DIR>
-__device__ __forceinline__ void mid_passes(float4 *s, const float2 *TN) {
-    using P = Plan<LOG2L>;
-    if (DIR < 0) {
-        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, -1>(s, TN); mid_sync<LOG2L>(); }
-        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, -1>(s, TN); mid_sync<LOG2L>(); }
-    } else {
-        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, +1>(s, TN); mid_sync<LOG2L>(); }
-        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, +1>(s, TN); mid_sync<LOG2L>(); }
-    }
-}
 
 // ---- K1: reference spectrum ------------------------------------------------------------------
 // grid = blocks to transform; refspec layout [slot][L] float4 {even.re, odd.re, even.im, odd.im}
@@ -175,15 +39,7 @@ k_ref_spectrum(const uint8_t *__restrict__ iq, size_t block_stride, const uint32
     pass1_from_global<LOG2L, true>(x, xormask, smem4, TN);
     __syncthreads();
     mid_passes<LOG2L, -1>(smem4, TN);
-    float4 *out = refspec + (size_t)slot * P::L;
-    constexpr int kTrips = (P::L / 2 + kFftThreads - 1) / kFftThreads;
-    for (int j = 0; j < kTrips; j++) {
-        const int m = pair_index<LOG2L>(j);
-        if (m >= P::L / 2) break;
-        const PC e0 = pc_from(smem4[ppad(2 * m)]), e1 = pc_from(smem4[ppad(2 * m + 1)]);
-        out[2 * m] = pc_to(pc_add(e0, e1));
-        out[2 * m + 1] = pc_to(pc_sub(e0, e1));
-    }
+    pair_out<LOG2L>(smem4, refspec + (size_t)slot * P::L);
 }
 
 // ---- K2: correlate one (block, channel) item ---------------------------------------------------
@@ -209,23 +65,7 @@ k_correlate(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, const uint
     __syncthreads();
     mid_passes<LOG2L, -1>(smem4, TN);
 
-    // last forward radix-2 stage, X * conj(R) (cdsp::conjugatemul, src/cdsp.cc:105-108),
-    // first inverse radix-2 stage -- all on adjacent pairs, in registers
-    constexpr int kTrips = (L / 2 + kFftThreads - 1) / kFftThreads;
-    for (int j = 0; j < kTrips; j++) {
-        const int m = pair_index<LOG2L>(j);
-        if (m >= L / 2) break;
-        // lanes 0-3 of every quarter-warp touch the even element first, lanes 4-7 the odd one:
-        // the eight 16-byte words of one LDS.128 / STS.128 phase then fall on distinct bank groups
-        const int sw = (threadIdx.x >> 2) & 1;
-        const float4 q0 = smem4[ppad(2 * m + sw)], q1 = smem4[ppad(2 * m + 1 - sw)];
-        const PC e0 = pc_from(sw ? q1 : q0), e1 = pc_from(sw ? q0 : q1);
-        const PC r0 = pc_from(__ldg(&R[2 * m])), r1 = pc_from(__ldg(&R[2 * m + 1]));
-        const PC z0 = pc_mulcp(pc_add(e0, e1), r0), z1 = pc_mulcp(pc_sub(e0, e1), r1);
-        const float4 o0 = pc_to(pc_add(z0, z1)), o1 = pc_to(pc_sub(z0, z1));
-        smem4[ppad(2 * m + sw)] = sw ? o1 : o0;
-        smem4[ppad(2 * m + 1 - sw)] = sw ? o0 : o1;
-    }
+    pair_correlate<LOG2L>(smem4, R);
     mid_sync<LOG2L>();
     mid_passes<LOG2L, +1>(smem4, TN);
     if constexpr (WarpLocal<LOG2L>::value) __syncthreads();
@@ -323,13 +163,15 @@ cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st) {
         case 11: return launch_ref_t<11>(p, st);
         case 12: return launch_ref_t<12>(p, st);
         case 13: return launch_ref_t<13>(p, st);
+        case 14: case 15: case 16: return launch_correlate_big(p, st);
         default: return cudaErrorInvalidValue;
     }
 }
 
 bool correlate_supported(uint32_t B) {
     uint32_t L = B / 2;
-    return (L & (L - 1)) == 0 && L >= 32 && L <= 8192;
+    return (L & (L - 1)) == 0 && L >= 32 && L <= 65536;
 }
+bool correlate_is_big(uint32_t B) { return B / 2 > 8192; }
 
 }  // namespace coh

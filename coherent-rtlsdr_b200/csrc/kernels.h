@@ -22,9 +22,14 @@ struct CorrLaunch {
     const uint32_t *block_slot;                              // block -> refspec slot (NULL = identity)
     uint32_t xormask;
     const float2 *TN; float2 *refspec; PeakRec *peaks;
+    // blocks above 8192 samples (fft_big.cu): HBM scratch [n_items][L] float4 and the twiddle
+    // table of the 8192-point sub-transforms
+    float4 *scratch; const float2 *TN_sub;
 };
 cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st);
+cudaError_t launch_correlate_big(const CorrLaunch &p, cudaStream_t st);
 bool correlate_supported(uint32_t B);
+bool correlate_is_big(uint32_t B);
 
 struct ApplyLaunch {
     const uint8_t *iq; uint32_t nch, B, n_blocks;     // n_blocks = whole batch (for the state hand-over)

@@ -40,7 +40,7 @@ typedef enum {
 
 typedef struct {
     uint32_t n_signal;          /* C, signal channels; the reference channel is extra         */
-    uint32_t blocksize;         /* B bytes per channel-block = 2L, power of two, 64..16384 for
+    uint32_t blocksize;         /* B bytes per channel-block = 2L, power of two, 64..131072 for
                                    the correlation path (src/main.cc:167 default 1<<14)       */
     uint32_t max_lag_slots;     /* reference: nfft-1 = 7 (src/ccoherent.cc:124); 0 = no cap   */
     float    alpha;             /* phase IIR weight; reference 0.5 (src/csdrdevice.cc:60)     */

@@ -21,7 +21,10 @@ def _rel_l2(a, b):
 
 
 @pytest.mark.parametrize("B,C,nb,shift", [(16384, 3, 6, False), (16384, 3, 6, True),
-                                          (2048, 5, 40, True), (512, 2, 70, False), (64, 1, 5, True)])
+                                          (2048, 5, 40, True), (512, 2, 70, False), (64, 1, 5, True),
+                                          # blocks above 8192 samples: the split transform of fft_big.cu
+                                          # (131072 bytes = BASELINE config 3's 65536-sample blocks)
+                                          (32768, 3, 4, False), (65536, 2, 3, True), (131072, 3, 3, True)])
 def test_sync_mode_matches_oracle(pkg, synth, oracle, B, C, nb, shift):
     L = B // 2
     maxd = min(250, L // 4)
