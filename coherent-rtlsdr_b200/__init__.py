@@ -16,7 +16,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libcoherent_cuda.so")
+# COHCUDA_LIB overrides the library path (kernel-variant experiments); default = the in-tree build
+LIB_PATH = os.environ.get("COHCUDA_LIB") or os.path.join(HERE, "lib", "libcoherent_cuda.so")
 
 LAG_NONE, LAG_ALL = 0, 1
 
