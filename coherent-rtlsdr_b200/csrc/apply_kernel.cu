@@ -430,10 +430,15 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
                     have = true; i0 = 1;
                 }
                 __syncwarp();
-                const float2 na2 = make_float2(na_w, na_w);
+                // csdrdevice.cc:67, each operation rounded on its own.  Scalar intrinsics on purpose:
+                // ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2, which changes the
+                // last bit whenever (1-alpha) is not a power of two.
 #pragma unroll 4
-                for (int i = i0; i < cnt; i++)          // csdrdevice.cc:67, each operation rounded on its own
-                    pp = __fadd2_rn(s_aq[i], __fmul2_rn(na2, pp));
+                for (int i = i0; i < cnt; i++) {
+                    const float2 aq = s_aq[i];
+                    pp.x = __fadd_rn(aq.x, __fmul_rn(na_w, pp.x));
+                    pp.y = __fadd_rn(aq.y, __fmul_rn(na_w, pp.y));
+                }
             }
             if (enabled) iir_step(pp, make_float2(__fmul_rn(a_w, q.x), __fmul_rn(a_w, q.y)), na_w);   // csdrdevice.cc:67
             if (lane == 0) {

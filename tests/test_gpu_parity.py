@@ -183,3 +183,20 @@ def test_cdsp_primitives_match_oracle(pkg, oracle):
             want = np.fft.fft(xi.astype(np.complex128), axis=1) if sign < 0 else np.fft.ifft(xi.astype(np.complex128), axis=1) * n
             assert np.linalg.norm(yo - want) / np.linalg.norm(want) < 2e-6
     eng.close()
+
+
+@pytest.mark.parametrize("alpha", [0.3, 0.9, 1.0])
+def test_iir_weight_other_than_reference_default(pkg, synth, oracle, alpha):
+    """alpha = 0.5 (src/csdrdevice.cc:60) makes every IIR product exact; other weights exercise
+    the individually rounded multiply and add of csdrdevice.cc:67 (no fused multiply-add) and the
+    look-back depth that follows from alpha."""
+    C, B, nb = 3, 2048, 150
+    iq, _ = synth.make_blocks(C, B, nb, seed=99, delays=np.array([0, 5, -9]))
+    noise = np.ones(nb, np.uint8); noise[40:47] = 0
+    eng = pkg.CoherentCuda(C, B, alpha=alpha, apply_shift=True)
+    out = eng.batch(iq, lag_mode=pkg.LAG_ALL, refnoise=noise)
+    cfg = oracle.make_config(C, B, alpha=alpha, apply_shift=1, int_dot=1)
+    ref = oracle.process_batch(cfg, iq, lag_mode=1, refnoise=noise)
+    np.testing.assert_array_equal(out["phase"].view(np.uint32), ref["phase"].view(np.uint32))
+    np.testing.assert_array_equal(out["packets"], ref["packets"])
+    eng.close()
