@@ -27,6 +27,16 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 C_SIG, BLOCKSIZE, N_BLOCKS = 21, 16384, 1024
+CONFIG = "ura21"
+# BASELINE.json configs other than the bench line (configs[1] = ura21), for BASELINE.md's table:
+#   --config four      configs[0]: four.cfg geometry, 3+1 channels x 8192 samples, 64 blocks
+#   --config big65536  configs[2]: 21+1 channels x 65536-sample blocks, resident chunk of 256 blocks
+#   --config stream    configs[4]: URA21 ring of 1024 blocks replayed; 1 % of the (block, channel) items
+#                      re-request a lag (drift re-sync), everything else tracks: use --mode mixed
+# configs[3] (168 channels, channel groups of 21 per GPU) is the ura21 line at --gpus 8 with_gather.
+PRESETS = {"ura21": (21, 16384, 1024), "four": (3, 16384, 64), "big65536": (21, 131072, 256),
+           "stream": (21, 16384, 1024)}
+REQ = None                        # host [n_blocks][C+1] lag-request flags for --mode mixed
 BYTES_PER_SAMPLE = 4.0            # 2 B u8 IQ in + 2 B int8 IQ out (packet mode)
 FLOP_PER_SAMPLE_SYNC = 311.0      # SURVEY 8d algorithmic flops per coherent sample, SYNC mode
 
@@ -209,6 +219,8 @@ def run_gpu_arm(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL's version / debug lines go to stdout by default: keep stdout for the ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -240,6 +252,7 @@ def run_gpu_arm(args):
 
     def step_dev(mode):
         eng.batch_raw(iq=iq.data_ptr(), iq_on_device=1, n_blocks=nb,
+                      lag_request=REQ if mode == "mixed" else None,
                       lag_mode=pkg.LAG_ALL if mode == "sync" else pkg.LAG_NONE,
                       refnoise_enabled=0 if args.no_refnoise else 1,
                       packets=pk_dev.data_ptr(), packets_on_device=1)
@@ -266,7 +279,7 @@ def run_gpu_arm(args):
     ms_main = timed(lambda: step_dev(args.mode), args.steps, args.warmup)
     launches = (eng.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
     clocks = sampler.stop() if rank == 0 else None
-    other = "track" if args.mode == "sync" else "sync"
+    other = "sync" if args.mode == "track" else "track"
     ms_other = timed(lambda: step_dev(other), args.steps, args.warmup)
 
     # per-kernel durations (CUDA events on the launching stream, one launch at a time)
@@ -278,22 +291,23 @@ def run_gpu_arm(args):
         p = eng.profile_read()
         eng.profile(False)
         return p
-    prof = {"sync": profile("sync"), "track": profile("track")}
+    prof = {m: profile(m) for m in {"sync", "track", args.mode}}
+    correlate_dominates = prof[args.mode]["k_correlate"]["ms"] > prof[args.mode]["k_apply"]["ms"]
 
     def roofline(mode):
-        if mode == "sync":
-            k = prof["sync"]["k_correlate"]; units = 2 * C_SIG * nb * L      # two profiled steps
+        if mode != "track" and correlate_dominates:
+            k = prof[mode]["k_correlate"]; units = 2 * C_SIG * nb * L      # two profiled steps
             name = "k_correlate"
         else:
-            k = prof["track"]["k_apply"]; units = 2 * nch * nb * L
+            k = prof[mode]["k_apply"]; units = 2 * nch * nb * L
             name = "k_apply"
         gbs = units * BYTES_PER_SAMPLE / (k["ms"] * 1e-3) / 1e9
-        traffic, traffic_src = ncu_traffic(name) if nb == N_BLOCKS else (None, None)
+        traffic, traffic_src = ncu_traffic(name) if (CONFIG == "ura21" and nb == 1024 and mode != "mixed") else (None, None)
         r = {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
              "frac": gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
              "launches_timed": k["launches"], "avg_launch_ms": k["ms"] / max(k["launches"], 1),
              "algorithmic_bytes_per_launch": units * BYTES_PER_SAMPLE / max(k["launches"], 1)}
-        if mode == "sync":
+        if mode == "sync" and L == 8192:
             r["fp32_tflops_algorithmic"] = units * FLOP_PER_SAMPLE_SYNC / (k["ms"] * 1e-3) / 1e12
         return r
 
@@ -306,6 +320,7 @@ def run_gpu_arm(args):
 
     def step_e2e():
         eng.batch_raw(iq=h_iq.data_ptr(), iq_on_device=0, n_blocks=nb,
+                      lag_request=REQ if args.mode == "mixed" else None,
                       lag_mode=pkg.LAG_ALL if args.mode == "sync" else pkg.LAG_NONE, refnoise_enabled=1,
                       packets=h_pk.data_ptr(), packets_on_device=0, lag=h_lag.data_ptr(),
                       mag=h_mag.data_ptr(), phasecorr=h_ph.data_ptr())
@@ -340,8 +355,9 @@ def run_gpu_arm(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_main / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"URA21: {C_SIG}+1 channels x {L}-sample blocks x {nb} blocks per GPU "
-                                   f"(BASELINE.json configs[1]), {args.mode.upper()} mode, software shift on",
+            "config": {"workload": f"{CONFIG}: {C_SIG}+1 channels x {L}-sample blocks x {nb} blocks per GPU "
+                                   f"(BASELINE.json configs[{list(PRESETS).index(CONFIG) if CONFIG != 'stream' else 4}]"
+                                   f"{' = URA21' if CONFIG == 'ura21' else ''}), {args.mode.upper()} mode, software shift on",
                        "mode": args.mode, "blocks_per_gpu": nb, "channels": nch, "L": L,
                        "parallelism": f"block-sharded x{world}, ref channel replicated",
                        "l2": f"input {nb * nch * B >> 20} MiB + output {nb * nch * B >> 20} MiB per step exceed the 126 MB L2 (no flush needed)"},
@@ -384,14 +400,24 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--mode", default="sync", choices=["sync", "track"])
-    ap.add_argument("--blocks", type=int, default=N_BLOCKS)
+    ap.add_argument("--mode", default="sync", choices=["sync", "track", "mixed"])
+    ap.add_argument("--config", default="ura21", choices=list(PRESETS))
+    ap.add_argument("--blocks", type=int, default=1024)
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--cpu-blocks", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--alpha", type=float, default=0.5, help="phase IIR weight (reference: 0.5)")
     ap.add_argument("--no-refnoise", action="store_true", help="diagnostic: noise source off (no phase estimate)")
     args = ap.parse_args()
+    global C_SIG, BLOCKSIZE, N_BLOCKS, CONFIG, REQ
+    CONFIG = args.config
+    C_SIG, BLOCKSIZE, N_BLOCKS = PRESETS[CONFIG]
+    if args.blocks == 1024:
+        args.blocks = N_BLOCKS
+    if args.mode == "mixed":
+        rng = np.random.default_rng(5)
+        REQ = (rng.random((args.blocks, C_SIG + 1)) < 0.01).astype(np.uint8)
+        REQ[0, 1:] = 1; REQ[:, 0] = 0
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         return run_reference_arm(args)
