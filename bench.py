@@ -130,17 +130,59 @@ def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=
 
 
 # ------------------------------------------------------------------ CPU baseline / reference arm
-def cpu_pass(O, iq, mode, threads):
-    """One pass of the CPU path over iq[nb][C+1][B]; returns seconds.  threads > 1 splits the
-    blocks into contiguous ranges, one oracle state per range (SURVEY BASELINE B2)."""
+# kind "reference": the reference's OWN translation units (oracle/_ref/libref_cdsp.so: cdsp.cc,
+# ccoherent.cc, csdrdevice.cc, crtlsdr.cc, cpacketizer.cc compiled unmodified against shims) fed
+# block by block through csdrdevice::swapbuffer -- its single DSP thread per process, as designed
+# (src/ccoherent.cc:245).  nfft = C+1 lets it correlate every channel of a block in SYNC mode (the
+# stock value 8 would measure only 7 channels per block).  kind "port": the C restatement
+# (oracle/liboracle.so), used only where the prebuilt reference library is absent.
+def _ref_worker(q_in, q_out, n_signal, B, mode, reps):
+    from oracle import oracle as O
+    iq = q_in.get()
+    nb = iq.shape[0]
+    req = np.zeros((nb, n_signal + 1), np.uint8)
+    if mode == "sync":
+        req[:, 1:] = 1
+    with O.RefCdsp(n_signal, B, nfft=n_signal + 1) as R:
+        R.run_batch(iq[:1], lag_request=req[:1])               # warm the instance up
+        q_out.put("ready"); q_in.get()                         # start line
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            R.run_batch(iq, lag_request=req)
+        q_out.put(time.perf_counter() - t0)
+
+
+def cpu_pass(O, iq, mode, threads, reps=1):
+    """`reps` passes of the CPU path over iq[nb][C+1][B] on `threads` host cores (contiguous block
+    ranges, one DSP thread / state per range); returns (seconds, kind)."""
     nb, nch, B = iq.shape
-    cfg = O.make_config(nch - 1, B)
-    lag_mode = 1 if mode == "sync" else 0
     ranges = [(i * nb // threads, (i + 1) * nb // threads) for i in range(threads)]
     ranges = [r for r in ranges if r[1] > r[0]]
+    if O.ref_available():
+        import multiprocessing as mp
+        ctx = mp.get_context("spawn")                          # one process per DSP thread (cpacketize is static)
+        procs = []
+        for r in ranges:
+            qi, qo = ctx.Queue(), ctx.Queue()
+            pr = ctx.Process(target=_ref_worker, args=(qi, qo, nch - 1, B, mode, reps), daemon=True)
+            pr.start(); qi.put(np.ascontiguousarray(iq[r[0]:r[1]]))
+            procs.append((pr, qi, qo))
+        for _, _, qo in procs:
+            assert qo.get(timeout=300) == "ready"
+        t0 = time.perf_counter()
+        for _, qi, _ in procs:
+            qi.put("go")
+        times = [qo.get(timeout=3600) for _, _, qo in procs]
+        wall = time.perf_counter() - t0
+        for pr, _, _ in procs:
+            pr.join(timeout=30)
+        return max(max(times), wall if threads > 1 else 0.0), "reference"
+    cfg = O.make_config(nch - 1, B)
+    lag_mode = 1 if mode == "sync" else 0
 
     def work(r):
-        O.process_batch(cfg, iq[r[0]:r[1]], lag_mode=lag_mode)
+        for _ in range(reps):
+            O.process_batch(cfg, iq[r[0]:r[1]], lag_mode=lag_mode)
 
     t0 = time.perf_counter()
     if len(ranges) == 1:
@@ -149,11 +191,7 @@ def cpu_pass(O, iq, mode, threads):
         ts = [threading.Thread(target=work, args=(r,)) for r in ranges]
         [t.start() for t in ts]
         [t.join() for t in ts]
-    return time.perf_counter() - t0
-
-
-def cpu_kind(O):
-    return "reference" if getattr(O, "ref_available", lambda: False)() else "port"
+    return time.perf_counter() - t0, "port"
 
 
 def run_reference_arm(args):
@@ -168,11 +206,9 @@ def run_reference_arm(args):
     # bounded sample of the workload: per step `sample_blocks` blocks of the URA21 geometry
     sample_blocks = args.cpu_blocks or (2 * cores if mode == "sync" else 16 * cores)
     iq, _ = synth.make_blocks(C_SIG, BLOCKSIZE, sample_blocks, seed=0xC0DE + 1)
-    for _ in range(args.warmup):
-        cpu_pass(O, iq[:max(cores, 1)], mode, cores)
-    t = 0.0
-    for _ in range(args.steps):
-        t += cpu_pass(O, iq, mode, cores)
+    if args.warmup:
+        cpu_pass(O, iq[:max(cores, 1)], mode, cores, reps=args.warmup)
+    t, kind = cpu_pass(O, iq, mode, cores, reps=args.steps)
     samples = (C_SIG + 1) * (BLOCKSIZE // 2) * sample_blocks * args.steps
     v = samples / t
     line = {
@@ -183,9 +219,9 @@ def run_reference_arm(args):
         "config": {"workload": f"URA21 {C_SIG}+1 ch x {BLOCKSIZE // 2} samples, {mode} mode, "
                                f"CPU sample of {sample_blocks} blocks/step (full workload {N_BLOCKS})",
                    "mode": mode},
-        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": cpu_kind(O),
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": kind,
                          "sample": f"{sample_blocks} blocks x {C_SIG + 1} channels per step, {args.steps} steps, "
-                                   f"{cores} threads over contiguous block ranges"},
+                                   f"{cores} DSP threads (one process each) over contiguous block ranges"},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -378,14 +414,15 @@ def run_gpu_arm(args):
         if world == 1 and not args.no_cpu:
             from oracle import oracle as O
             synth = cohpkg.synth()
-            probe, _ = synth.make_blocks(C_SIG, B, 8, seed=0xC0DE + 1)
-            t_probe = cpu_pass(O, probe, args.mode, 1)
-            n_cpu = int(min(max(8, 8 * args.cpu_seconds / max(t_probe, 1e-6)), 2048))
+            probe, _ = synth.make_blocks(C_SIG, B, 4, seed=0xC0DE + 1)
+            t_probe, _ = cpu_pass(O, probe, args.mode, 1)
+            n_cpu = int(min(max(4, 4 * args.cpu_seconds / max(t_probe, 1e-6)), 2048))
             cpu_iq, _ = synth.make_blocks(C_SIG, B, n_cpu, seed=0xC0DE + 1)
-            t_cpu = cpu_pass(O, cpu_iq, args.mode, 1)
+            t_cpu, kind = cpu_pass(O, cpu_iq, args.mode, 1)
             line["cpu_baseline"] = {"value": nch * L * n_cpu / t_cpu, "unit": "samples/s", "cores": 1,
-                                    "kind": cpu_kind(O),
-                                    "sample": f"{n_cpu} blocks x {nch} channels of the same workload, {args.mode} mode, "
+                                    "kind": kind,
+                                    "sample": f"{n_cpu} blocks x {nch} channels of the same workload, "
+                                              f"{'track' if args.mode == 'mixed' else args.mode} mode, "
                                               f"1 thread (the reference's single DSP thread), {t_cpu:.1f} s"}
         print(json.dumps(line))
     eng.close()
