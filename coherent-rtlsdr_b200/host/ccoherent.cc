@@ -193,6 +193,12 @@ void ccoherent::threadf(ccoherent *ctx)
         e->chan[0] = (const uint8_t *)refsptr;
         e->readcnt[0] = ctx->refdev->get_readcntbuf();
         e->request[0] = 0; e->ready[0] = 1;
+        // A lag is only measured on blocks taken from the head of the rings.  While the thread works
+        // off a backlog (start-up: the rings fill while the engine is created, as they do in the
+        // reference while FFTW plans) a slot can be overwritten between the reads of two devices,
+        // and a correlation across ring generations returns a meaningless peak that sends the
+        // controller slewing the wrong way for seconds.  The request stays pending until then.
+        const bool ref_at_head = ctx->refdev->newdata.load() == 0;
         pin_once(e, refsptr, B);
         ctx->queuelag(ctx->refdev);                                        // slot 0 (:253)
 
@@ -208,7 +214,7 @@ void ccoherent::threadf(ccoherent *ctx)
             e->request[k] = 0;
             if (ready) {
                 pin_once(e, ptr, B);
-                if (d->is_lagrequested()) {                                // :266-267
+                if (d->is_lagrequested() && ref_at_head && d->newdata.load() == 0) {   // :266-267
                     const size_t before = ctx->lagqueuesize();
                     ctx->queuelag(d);
                     e->request[k] = ctx->lagqueuesize() > before;

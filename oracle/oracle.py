@@ -202,6 +202,15 @@ def ref_lib(path=None):
         L.refh_cdsp_conjugatemul.argtypes = [vp, vp, vp, i]
         L.refh_cdsp_indexofmax.argtypes = [vp, i]
         L.refh_cdsp_indexofmax.restype = C.c_uint32
+        if hasattr(L, "refh_live_create"):
+            L.refh_live_create.restype = vp
+            L.refh_live_create.argtypes = [u32, u32, u32, vp, vp, vp, C.c_uint64, i]
+            L.refh_live_poll.restype = C.c_uint64
+            L.refh_live_poll.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+            L.refh_live_kick.argtypes = [vp, u32, C.c_double]
+            L.refh_live_last_packet.restype = C.c_size_t
+            L.refh_live_last_packet.argtypes = [vp, vp, C.c_size_t]
+            L.refh_live_destroy.argtypes = [vp]
         _ref[path] = L
     return _ref[path]
 
@@ -253,3 +262,54 @@ class RefCdsp:
             self.close()
         except Exception:
             pass
+
+
+class RefLive:
+    """The reference's whole object graph free-running against simulated dongles (live mode of
+    oracle/ref_harness.cc): read threads, ccontrol threads, DSP thread, sender.  The fake
+    librtlsdr's delay follows the correction ccontrol sets (oracle/shim/shim_impl.cc), so the
+    loop lag -> ppm law -> resampler -> delay is closed.  With lib_path=DROPIN_LIB_PATH the DSP
+    thread is the product's host/ccoherent.cc on the GPU; everything else is unchanged."""
+
+    def __init__(self, delays, blocksize=16384, fs=1024000, gains=None, phases=None, seed=0xC0DE, nfft=8,
+                 lib_path=None):
+        self.lib = ref_lib(lib_path)
+        n_signal = len(delays)
+        self.nch, self.B = n_signal + 1, blocksize
+        d0 = np.zeros(self.nch, dtype=np.float64); d0[1:] = delays
+        g = np.ones(self.nch, dtype=np.float32)
+        ph = np.zeros(self.nch, dtype=np.float32)
+        if gains is not None: g[1:] = gains
+        if phases is not None: ph[1:] = phases
+        self.h = self.lib.refh_live_create(n_signal, blocksize, fs, _p(d0), _p(g), _p(ph), seed, nfft)
+        if not self.h:
+            raise RuntimeError("refh_live_create failed (another instance live, or bad geometry)")
+
+    def poll(self):
+        out = {"lag": np.zeros(self.nch, dtype=np.float32), "synced": np.zeros(self.nch, dtype=np.uint8),
+               "delay": np.zeros(self.nch, dtype=np.float64), "corr": np.zeros(self.nch, dtype=np.float32),
+               "n_corrections": np.zeros(self.nch, dtype=np.uint32), "blocks": np.zeros(self.nch, dtype=np.uint64)}
+        out["packets"] = self.lib.refh_live_poll(self.h, _p(out["lag"]), _p(out["synced"]), _p(out["delay"]),
+                                                 _p(out["corr"]), _p(out["n_corrections"]), _p(out["blocks"]))
+        return out
+
+    def kick(self, chan, delta):
+        if self.lib.refh_live_kick(self.h, chan, float(delta)):
+            raise ValueError("bad channel")
+
+    def last_packet(self):
+        n = self.lib.refh_live_last_packet(self.h, None, 0)
+        buf = np.zeros(n, dtype=np.uint8)
+        self.lib.refh_live_last_packet(self.h, _p(buf), n)
+        return buf
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.refh_live_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()

@@ -206,6 +206,157 @@ void refh_destroy(void *hv)
     delete h;
 }
 
+/* ---- live mode: the whole object graph free-running against the simulated dongles ---------
+ * Everything main() starts (src/main.cc:226-279) is started for real: the per-device read threads
+ * (crtlsdr::start -> rtlsdr_read_async -> asynch_callback -> swapbuffer), the per-device
+ * controllers (ccontrol::threadf, the ppm law of src/ccontrol.cc:73-123), the DSP thread
+ * (ccoherent::threadf) and a sender looping cpacketize::send().  The fake librtlsdr in
+ * shim_impl.cc is a replay source whose delay moves with the correction the controller sets, so
+ * the loop closes: lag measured by the path -> ccontrol -> resampler -> delay -> next lag.
+ * Start order as in main(): devices, then ccoherent once the rings have filled.                */
+extern "C" void orc_sim_configure(uint32_t n_dev, const double *delay0, const float *gain, const float *phase,
+                                  double fs, uint64_t seed);
+extern "C" void orc_sim_off(void);
+extern "C" int orc_sim_get(uint32_t index, double *delay, float *corr, uint64_t *blocks, uint32_t *n_corrections);
+extern "C" int orc_sim_kick(uint32_t index, double delta);
+
+namespace {
+struct LiveHarness {
+    uint32_t C = 0, B = 0, nch = 0;
+    crefsdr *ref = nullptr;
+    lvector<csdrdevice *> devs;
+    crefnoise *noise = nullptr;
+    ccoherent *coh = nullptr;
+    barrier *bar = nullptr;
+    std::thread sender;
+    std::atomic<bool> stop{ false };
+    std::atomic<uint64_t> packets{ 0 };
+    std::mutex pm;
+    std::vector<uint8_t> last_packet;
+    crtlsdr *dev(uint32_t c) { return c == 0 ? (crtlsdr *)ref : (crtlsdr *)devs[c - 1]; }
+};
+LiveHarness *g_livesim = nullptr;
+}  // namespace
+
+void *refh_live_create(uint32_t n_signal, uint32_t blocksize, uint32_t fs, const double *delay0, const float *gain,
+                       const float *phase, uint64_t seed, int nfft)
+{
+    if (g_live || g_livesim || n_signal == 0 || blocksize < 16 || (blocksize & (blocksize - 1))) return nullptr;
+    LiveHarness *h = new LiveHarness;
+    h->C = n_signal; h->B = blocksize; h->nch = n_signal + 1;
+    orc_sim_configure(h->nch, delay0, gain, phase, (double)fs, seed);
+    const uint32_t fc = 1024000000u, asyncbufn = 8;
+    h->noise = new crefnoise("/dev/null");
+    h->noise->enabled = true;
+    h->ref = new crefsdr(asyncbufn, blocksize, fs, fc);
+    h->ref->open(0u);
+    for (uint32_t k = 0; k < n_signal; k++) {
+        h->devs.push_back(new crtlsdr(asyncbufn, blocksize, fs, fc));
+        h->devs.back()->open(k + 1);
+    }
+    cpacketize::globalseqn = 0;
+    cpacketize::bufferfilled = false;
+    cpacketize::do_exit = false;
+    cpacketize::init("tcp://*:5555", false, h->nch, blocksize);
+    h->sender = std::thread([h] {
+        while (!h->stop.load()) {
+            cpacketize::send();                                      /* src/main.cc:277-279 */
+            if (h->stop.load()) break;
+            std::lock_guard<std::mutex> lock(h->pm);
+            h->last_packet = cpacketize::socket->last;
+            h->packets++;
+        }
+    });
+    h->bar = new barrier(h->nch);
+    h->ref->start(h->bar);
+    for (uint32_t k = 0; k < n_signal; k++) h->devs[k]->start(h->bar);   /* read thread + controller */
+    /* main() constructs ccoherent after the devices were started, and its FFTW_MEASURE planning
+     * outlasts the first asyncbufn blocks: the DSP thread first runs with every ring full, which
+     * is what keeps the signal rings block-aligned with the reference ring (threadf does not
+     * consume() from a device that is not is_ready(), src/ccoherent.cc:262-281).  Made explicit: */
+    for (uint32_t c = 0; c < h->nch; c++)
+        while (h->dev(c)->get_readcnt() < asyncbufn) std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    h->coh = new ccoherent(h->ref, &h->devs, h->noise, nfft);
+    h->coh->start();
+    g_livesim = h;
+    return h;
+}
+
+/* per channel (entry 0 = reference): last published lag, synced flag, the simulator's true delay,
+ * the correction in force, how many corrections the controller has issued; returns packets sent */
+uint64_t refh_live_poll(void *hv, float *lag, uint8_t *synced, double *delay, float *corr, uint32_t *n_corrections,
+                        uint64_t *blocks)
+{
+    LiveHarness *h = (LiveHarness *)hv;
+    if (!h || h != g_livesim) return 0;
+    for (uint32_t c = 0; c < h->nch; c++) {
+        if (lag) lag[c] = c ? h->dev(c)->get_lagp()->lag : 0.0f;
+        if (synced) synced[c] = c ? (h->dev(c)->get_synchronized() ? 1 : 0) : 1;
+        orc_sim_get(c, delay ? delay + c : nullptr, corr ? corr + c : nullptr, blocks ? blocks + c : nullptr,
+                    n_corrections ? n_corrections + c : nullptr);
+    }
+    return h->packets.load();
+}
+
+/* an external delay step on one channel and, as the console's `sync` command does
+ * (src/console.cc:285-289), the synced flag dropped so the controller re-acquires */
+int refh_live_kick(void *hv, uint32_t chan, double delta)
+{
+    LiveHarness *h = (LiveHarness *)hv;
+    if (!h || h != g_livesim || chan == 0 || chan >= h->nch) return -1;
+    orc_sim_kick(chan, delta);
+    /* the source works one block ahead: let the step reach the DSP thread before asking */
+    const uint64_t seen = h->packets.load();
+    while (h->packets.load() < seen + 3) std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    h->dev(chan)->set_synchronized(false);
+    return 0;
+}
+
+size_t refh_live_last_packet(void *hv, uint8_t *out, size_t cap)
+{
+    LiveHarness *h = (LiveHarness *)hv;
+    if (!h || h != g_livesim) return 0;
+    std::lock_guard<std::mutex> lock(h->pm);
+    const size_t n = h->last_packet.size() < cap ? h->last_packet.size() : cap;
+    if (out && n) std::memcpy(out, h->last_packet.data(), n);
+    return h->last_packet.size();
+}
+
+void refh_live_destroy(void *hv)
+{
+    LiveHarness *h = (LiveHarness *)hv;
+    if (!h || h != g_livesim) return;
+    /* controllers first, while blocks still flow: a controller parked in wait_synchronized() or
+     * requestfftblocking() needs the DSP thread alive to come back and see do_exit */
+    for (uint32_t k = 0; k < h->C; k++) {
+        h->devs[k]->controller->request_exit();
+        h->devs[k]->set_synchronized(false);
+    }
+    for (uint32_t k = 0; k < h->C; k++) h->devs[k]->controller->join();
+    h->coh->request_exit();
+    h->coh->join();                              /* sees do_exit at the next block */
+    delete h->coh;
+    h->stop = true;
+    cpacketize::do_exit = true;
+    cpacketize::cv.notify_all();
+    h->sender.join();
+    for (uint32_t c = 0; c < h->nch; c++) {      /* crtlsdr::stop() minus its raise(SIGUSR1) */
+        rtlsdr_cancel_async(h->dev(c)->dev);
+        h->dev(c)->streaming = false;
+        h->dev(c)->cv.notify_all();
+    }
+    for (uint32_t c = 0; c < h->nch; c++) if (h->dev(c)->thread.joinable()) h->dev(c)->thread.join();
+    for (uint32_t c = 0; c < h->nch; c++) h->dev(c)->close();
+    for (uint32_t k = 0; k < h->C; k++) delete h->devs[k];
+    delete h->ref;
+    cpacketize::cleanup();
+    delete h->noise;
+    delete h->bar;
+    orc_sim_off();
+    g_livesim = nullptr;
+    delete h;
+}
+
 /* ---- the reference's cdsp:: statics, called directly (src/cdsp.cc) ------------------------ */
 void refh_cdsp_convtosigned(const uint8_t *in, uint8_t *out, int n) { cdsp::convtosigned(in, out, n); }
 void refh_cdsp_convtofloat(float *out, const int8_t *s8, int n) { cdsp::convtofloat(out, s8, n); }

@@ -18,6 +18,8 @@
 
 #include <atomic>
 #include <chrono>
+#include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -162,13 +164,119 @@ extern "C" void fftwf_execute(const fftwf_plan p) { fftwf_execute_dft(p, p->in, 
 extern "C" void fftwf_destroy_plan(fftwf_plan p) { delete p; }
 
 /* ---------------------------------------------------------------------------- librtlsdr ---- */
+/*
+ * Two modes.  Lock-step (default): rtlsdr_read_async parks and the harness pushes blocks through
+ * csdrdevice::swapbuffer itself.  Replay/simulation (orc_sim_configure): every opened device is a
+ * live source -- rtlsdr_read_async calls the reference's callback (crtlsdr::asynch_callback,
+ * src/crtlsdr.cc:62-68) once per block period from a ring of buf_num buffers, the way librtlsdr
+ * does -- with
+ *     x_k[t] = g_k e^{j phi_k} r[t - round(d_k)] + w_k[t],   device 0: x_0 = r   (SURVEY 8d input)
+ * r, w counter-hashed Gaussians (any t is addressable, so delays may be negative), and the
+ * resampler model the reference's controller relies on (src/ccontrol.cc:96-116: after a
+ * correction f held for a time t the delay has moved by f*fs*t samples):
+ *     d_k  <-  d_k - f_k * L        once per block of L samples,
+ * f_k the last value passed to rtlsdr_set_sample_freq_correction_f.  Pacing is wall-clock
+ * (block period L/fs) because ccontrol sleeps on the wall clock.
+ */
 struct rtlsdr_dev {
     uint32_t index;
     std::atomic<bool> cancel{ false };
     std::mutex m;
     std::vector<float> corrections;          /* every rtlsdr_set_sample_freq_correction_f value */
+    std::atomic<float> corr{ 0.0f };         /* the one in force */
+    std::atomic<double> delay{ 0.0 };
+    std::atomic<uint64_t> blocks{ 0 };
+    float gain = 1.0f, phase = 0.0f;
 };
 static const uint32_t kFakeDevices = 256;
+
+namespace {
+struct OrcSim {
+    std::mutex m;
+    bool on = false;
+    double fs = 0.0;
+    uint64_t seed = 0;
+    std::vector<double> delay0;
+    std::vector<float> gain, phase;
+    bool t0_set = false;
+    std::chrono::steady_clock::time_point t0;
+    rtlsdr_dev *open_dev[kFakeDevices] = {};
+} g_sim;
+
+inline uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+/* two unit-variance near-Gaussians (Irwin-Hall of four 16-bit uniforms each) per counter value */
+inline void gauss_pair(uint64_t stream, int64_t t, float &a, float &b)
+{
+    const uint64_t h0 = splitmix64(stream ^ (uint64_t)t * 0xD1342543DE82EF95ull), h1 = splitmix64(h0);
+    const float k = 1.0f / 37837.2f;         /* sqrt(4 * 65536^2 / 12) */
+    a = ((float)((h0 & 0xffff) + ((h0 >> 16) & 0xffff) + ((h0 >> 32) & 0xffff) + (h0 >> 48)) - 131070.0f) * k;
+    b = ((float)((h1 & 0xffff) + ((h1 >> 16) & 0xffff) + ((h1 >> 32) & 0xffff) + (h1 >> 48)) - 131070.0f) * k;
+}
+inline uint8_t quantise(float v)
+{
+    float q = std::nearbyint(v + 127.5f);
+    return (uint8_t)(q < 0.0f ? 0.0f : (q > 255.0f ? 255.0f : q));
+}
+void sim_fill(rtlsdr_dev *dev, uint8_t *buf, uint32_t len, uint64_t n)
+{
+    const uint32_t L = len / 2;
+    const int64_t d = (int64_t)std::llround(dev->delay.load());
+    const uint64_t rs = g_sim.seed, ws = splitmix64(g_sim.seed + 1 + dev->index);
+    const float cr = dev->gain * std::cos(dev->phase), ci = dev->gain * std::sin(dev->phase);
+    for (uint32_t i = 0; i < L; i++) {
+        const int64_t t = (int64_t)(n * L) + i;
+        float rr, ri;
+        gauss_pair(rs, t - d, rr, ri);
+        rr *= 40.0f; ri *= 40.0f;
+        float xr = rr, xi = ri;
+        if (dev->index != 0) {
+            float wr, wi;
+            gauss_pair(ws, t, wr, wi);
+            xr = cr * rr - ci * ri + 4.0f * wr;
+            xi = cr * ri + ci * rr + 4.0f * wi;
+        }
+        buf[2 * i] = quantise(xr); buf[2 * i + 1] = quantise(xi);
+    }
+}
+}  // namespace
+
+/* n_dev devices (index 0 = reference); delay0/gain/phase per device (entry 0 ignored) */
+extern "C" void orc_sim_configure(uint32_t n_dev, const double *delay0, const float *gain, const float *phase,
+                                  double fs, uint64_t seed)
+{
+    std::lock_guard<std::mutex> lock(g_sim.m);
+    g_sim.on = n_dev > 0; g_sim.fs = fs; g_sim.seed = seed; g_sim.t0_set = false;
+    g_sim.delay0.assign(delay0, delay0 + n_dev);
+    g_sim.gain.assign(gain, gain + n_dev);
+    g_sim.phase.assign(phase, phase + n_dev);
+}
+extern "C" void orc_sim_off(void) { std::lock_guard<std::mutex> lock(g_sim.m); g_sim.on = false; }
+extern "C" int orc_sim_get(uint32_t index, double *delay, float *corr, uint64_t *blocks, uint32_t *n_corrections)
+{
+    std::lock_guard<std::mutex> lock(g_sim.m);
+    rtlsdr_dev *d = index < kFakeDevices ? g_sim.open_dev[index] : nullptr;
+    if (!d) return -1;
+    if (delay) *delay = d->delay.load();
+    if (corr) *corr = d->corr.load();
+    if (blocks) *blocks = d->blocks.load();
+    if (n_corrections) { std::lock_guard<std::mutex> l2(d->m); *n_corrections = (uint32_t)d->corrections.size(); }
+    return 0;
+}
+/* a delay step injected from outside (cable swap / dropped USB transfer), for re-sync tests */
+extern "C" int orc_sim_kick(uint32_t index, double delta)
+{
+    std::lock_guard<std::mutex> lock(g_sim.m);
+    rtlsdr_dev *d = index < kFakeDevices ? g_sim.open_dev[index] : nullptr;
+    if (!d) return -1;
+    d->delay.store(d->delay.load() + delta);
+    return 0;
+}
 
 extern "C" uint32_t rtlsdr_get_device_count(void) { return kFakeDevices; }
 extern "C" const char *rtlsdr_get_device_name(uint32_t) { return "oracle fake RTL-SDR"; }
@@ -182,10 +290,25 @@ extern "C" int rtlsdr_get_device_usb_strings(uint32_t index, char *manufact, cha
 extern "C" int rtlsdr_get_index_by_serial(const char *serial) { return serial ? atoi(serial) : -1; }
 extern "C" int rtlsdr_open(rtlsdr_dev_t **dev, uint32_t index)
 {
-    *dev = new rtlsdr_dev; (*dev)->index = index;
+    rtlsdr_dev *d = new rtlsdr_dev; d->index = index;
+    std::lock_guard<std::mutex> lock(g_sim.m);
+    if (g_sim.on && index < g_sim.delay0.size()) {
+        d->delay = index ? g_sim.delay0[index] : 0.0;
+        d->gain = g_sim.gain[index]; d->phase = g_sim.phase[index];
+    }
+    if (index < kFakeDevices) g_sim.open_dev[index] = d;
+    *dev = d;
     return 0;
 }
-extern "C" int rtlsdr_close(rtlsdr_dev_t *dev) { delete dev; return 0; }
+extern "C" int rtlsdr_close(rtlsdr_dev_t *dev)
+{
+    {
+        std::lock_guard<std::mutex> lock(g_sim.m);
+        if (dev->index < kFakeDevices && g_sim.open_dev[dev->index] == dev) g_sim.open_dev[dev->index] = nullptr;
+    }
+    delete dev;
+    return 0;
+}
 extern "C" int rtlsdr_set_center_freq(rtlsdr_dev_t *, uint32_t) { return 0; }
 extern "C" int rtlsdr_set_sample_rate(rtlsdr_dev_t *, uint32_t) { return 0; }
 extern "C" int rtlsdr_set_agc_mode(rtlsdr_dev_t *, int) { return 0; }
@@ -196,13 +319,37 @@ extern "C" int rtlsdr_set_sample_freq_correction_f(rtlsdr_dev_t *dev, float ppm)
 {
     std::lock_guard<std::mutex> lock(dev->m);
     dev->corrections.push_back(ppm);
+    dev->corr = ppm;
     return 0;
 }
 extern "C" int rtlsdr_reset_buffer(rtlsdr_dev_t *) { return 0; }
-extern "C" int rtlsdr_read_async(rtlsdr_dev_t *dev, rtlsdr_read_async_cb_t, void *, uint32_t, uint32_t)
+extern "C" int rtlsdr_read_async(rtlsdr_dev_t *dev, rtlsdr_read_async_cb_t cb, void *ctx, uint32_t buf_num, uint32_t buf_len)
 {
-    /* no USB: the harness delivers blocks through csdrdevice::swapbuffer; park until cancelled */
-    while (!dev->cancel.load()) std::this_thread::sleep_for(std::chrono::milliseconds(2));
+    bool live; double fs; std::chrono::steady_clock::time_point t0;
+    {
+        std::lock_guard<std::mutex> lock(g_sim.m);
+        live = g_sim.on && dev->index < g_sim.delay0.size() && cb && buf_num && buf_len;
+        if (live && !g_sim.t0_set) { g_sim.t0 = std::chrono::steady_clock::now(); g_sim.t0_set = true; }
+        fs = g_sim.fs; t0 = g_sim.t0;
+    }
+    if (!live) {
+        /* no USB: the harness delivers blocks through csdrdevice::swapbuffer; park until cancelled */
+        while (!dev->cancel.load()) std::this_thread::sleep_for(std::chrono::milliseconds(2));
+        return 0;
+    }
+    std::vector<uint8_t> ring((size_t)buf_num * buf_len);
+    const uint32_t L = buf_len / 2;
+    const double period = (double)L / fs;
+    for (uint64_t n = 0; !dev->cancel.load(); n++) {
+        if (dev->index) dev->delay.store(dev->delay.load() - (double)dev->corr.load() * (double)L);
+        uint8_t *buf = ring.data() + (size_t)(n % buf_num) * buf_len;
+        sim_fill(dev, buf, buf_len, n);
+        std::this_thread::sleep_until(t0 + std::chrono::duration_cast<std::chrono::steady_clock::duration>(
+                                               std::chrono::duration<double>((double)(n + 1) * period)));
+        if (dev->cancel.load()) break;
+        cb(buf, buf_len, ctx);
+        dev->blocks = n + 1;
+    }
     return 0;
 }
 extern "C" int rtlsdr_cancel_async(rtlsdr_dev_t *dev) { dev->cancel = true; return 0; }

@@ -1,0 +1,88 @@
+"""Closed-loop acquisition: the reference's whole object graph running
+free against simulated dongles.
+
+Everything main() starts is started for real (oracle/ref_harness.cc, live mode): the per-device
+read threads (crtlsdr::start -> rtlsdr_read_async -> asynch_callback -> swapbuffer), the per-device
+controllers (ccontrol::threadf: requestfftblocking -> lag -> maxppm*tanh(lag/100) held for
+0.9*|lag/(p*fs)| s, src/ccontrol.cc:73-123), the DSP thread and the sender.  The fake librtlsdr
+(oracle/shim/shim_impl.cc) is a replay source whose delay moves with the correction the controller
+sets, so the only scalar outputs of the hot path -- lag and the synced flag -- close a real loop.
+
+CPU variant: the reference's own src/ccoherent.cc / src/cdsp.cc (validates the simulator).
+GPU variant: the same graph with host/ccoherent.cc + host/cdsp.cc over libcoherent_cuda.so.
+"""
+import time
+
+import numpy as np
+import pytest
+
+DELAYS = [120.0, -35.0, 4.0]
+PHASES = [0.3, -1.0, 2.0]
+GAINS = [0.9, 0.8, 0.7]
+
+
+def _acquire(oracle, lib_path, timeout=20.0):
+    """Runs until every channel reports synced; returns the poll history and the last packet."""
+    hist = []
+    with oracle.RefLive(DELAYS, blocksize=16384, fs=1024000, gains=GAINS, phases=PHASES, lib_path=lib_path) as lv:
+        t0 = time.time()
+        while time.time() - t0 < timeout:
+            time.sleep(0.05)
+            hist.append(lv.poll())
+            if hist[-1]["synced"].all():
+                break
+        # a delay step on channel 2 + the console's `sync` (src/console.cc:285-289): re-acquisition
+        lv.kick(2, 57.0)
+        t1 = time.time()
+        rehist = []
+        while time.time() - t1 < timeout:
+            time.sleep(0.05)
+            rehist.append(lv.poll())
+            if rehist[-1]["synced"].all() and abs(rehist[-1]["delay"][2]) < 0.75:
+                break
+        time.sleep(0.1)
+        final = lv.poll()
+        pkt = lv.last_packet()
+    return hist, rehist, final, pkt
+
+
+def _check(hist, rehist, final, pkt):
+    nch, B = len(DELAYS) + 1, 16384
+    assert hist[-1]["synced"].all(), f"not synchronised: {hist[-1]}"
+    # the law's sign: the correction has the sign of the measured lag, and -- whenever that lag was
+    # a valid measurement of the true delay -- drives the delay towards zero (d -= corr * L)
+    for h in hist + rehist:
+        for c in range(1, nch):
+            if h["corr"][c] != 0:
+                assert np.sign(h["corr"][c]) == np.sign(h["lag"][c]), h
+    # residual delay below half a sample everywhere: an integer lag of 0 is all the path can see
+    assert np.abs(final["delay"][1:]).max() < 0.75, final["delay"]
+    assert (final["lag"][1:] == 0).all()
+    assert (final["corr"][1:] == 0).all()                       # set_correction_f(0) on sync
+    assert rehist[-1]["synced"].all(), f"re-sync failed: {rehist[-1]}"
+    assert any(abs(h["lag"][2]) > 20 for h in rehist), "the kick was never measured"
+    # the stream kept flowing and the last packet is a well-formed hdr0 packet (cpacketizer.h:32-37)
+    assert final["packets"] > 50
+    hdr = pkt[:16].view(np.uint32)
+    assert hdr[1] == nch and hdr[2] == B // 2 and hdr[3] == 0
+    assert len(pkt) == 16 + 4 * nch + 2 * nch * B               # the 2x packetlen quirk (cpacketizer.cc:91-96)
+    body = pkt[16 + 4 * nch:16 + 4 * nch + nch * B].view(np.int8).reshape(nch, B // 2, 2).astype(np.float32)
+    z = body[..., 0] + 1j * body[..., 1]
+    # synchronised and phase-corrected: every column lines up with the reference column
+    for c in range(1, nch):
+        rho = np.vdot(z[0], z[c]) / np.sqrt(np.vdot(z[0], z[0]).real * np.vdot(z[c], z[c]).real)
+        assert abs(rho) > 0.9, (c, rho)
+        assert abs(np.angle(rho)) < 0.05, (c, np.angle(rho))
+
+
+def test_reference_control_loop_converges_on_simulated_dongles(oracle):
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref/libref_cdsp.so not built (needs /root/reference)")
+    _check(*_acquire(oracle, None))
+
+
+@pytest.mark.gpu
+def test_dropin_gpu_path_closes_the_reference_control_loop(oracle):
+    if not oracle.dropin_available():
+        pytest.fail("oracle/_ref/libdropin_cuda.so is missing: run __graft_entry__.build() where /root/reference exists")
+    _check(*_acquire(oracle, oracle.DROPIN_LIB_PATH))
