@@ -61,13 +61,19 @@ k_correlate(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, const uint
     const uint32_t slot = block_slot ? block_slot[b] : b;
     const float4 *R = refspec + (size_t)slot * L;
 
-    pass1_from_global<LOG2L, false>(x, xormask, smem4, TN);
+    // per-thread twiddle bases of all passes, fetched once ahead of the barriers
+    static_assert(S <= kFftThreads, "one butterfly per thread in every pass");
+    const int tlow = threadIdx.x < S ? threadIdx.x : 0;
+    const float2 w_l = __ldg(&TN[2 * tlow]), w_n = __ldg(&TN[tlow]);   // W_L^low, W_N^low
+    const MidTw mt = mid_twiddles<LOG2L>(TN);
+
+    pass1_from_global<LOG2L, false>(x, xormask, smem4, w_l, w_n);
     __syncthreads();
-    mid_passes<LOG2L, -1>(smem4, TN);
+    mid_passes<LOG2L, -1>(smem4, mt);
 
     pair_correlate<LOG2L>(smem4, R);
     mid_sync<LOG2L>();
-    mid_passes<LOG2L, +1>(smem4, TN);
+    mid_passes<LOG2L, +1>(smem4, mt);
     if constexpr (WarpLocal<LOG2L>::value) __syncthreads();
 
     // last inverse pass (radix 16, stride L/16) kept in registers; recombine the halves,
@@ -77,7 +83,7 @@ k_correlate(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, const uint
     for (int low = threadIdx.x; low < S; low += kFftThreads) {
         PC v[16];
         {
-            const TwPair tw(cconj(__ldg(&TN[2 * low])), cconj(__ldg(&TN[low])));
+            const TwPair tw(cconj(w_l), cconj(w_n));
 #pragma unroll
             for (int k = 0; k < 16; k++) v[k] = tw.apply(pc_from(smem4[ppad(low + k * S)]), k);
         }

@@ -65,38 +65,70 @@ struct TwPair {
 
 // ---- pass 1: global bytes -> shared, radix 16 at stride L/16, both halves ------------------
 template <int LOG2L, bool NEG_B>
+__device__ __forceinline__ void pass1_butterfly(const uint8_t *x, uint32_t xormask, float4 *s, int low,
+                                                float2 w_l, float2 w_n) {
+    constexpr int S = Plan<LOG2L>::S1;
+    PC v[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const float2 a = load_sample(x, low + k * S, xormask);
+        const float2 b = mul_w32<-1>(a, k);           // W_N^(k*L/16) = W_32^k
+        v[k].r = make_float2(a.x, b.x); v[k].i = make_float2(a.y, b.y);
+    }
+    PDft<16, -1>::run(v);
+    float2 g = w_n;                                   // W_N^low (odd-bin modulation)
+    if (NEG_B) g = make_float2(-g.x, -g.y);           // ref sits in [L,2L): odd bins change sign
+    const TwPair tw(w_l, g);                          // W_L^low
+#pragma unroll
+    for (int k = 0; k < 16; k++) s[ppad(low + k * S)] = pc_to(tw.apply(v[k], k));
+}
+template <int LOG2L, bool NEG_B>
 __device__ __forceinline__ void pass1_from_global(const uint8_t *x, uint32_t xormask, float4 *s,
                                                   const float2 *__restrict__ TN) {
-    using P = Plan<LOG2L>;
-    constexpr int S = P::S1;
-    for (int low = threadIdx.x; low < S; low += kFftThreads) {
-        PC v[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            const float2 a = load_sample(x, low + k * S, xormask);
-            const float2 b = mul_w32<-1>(a, k);       // W_N^(k*L/16) = W_32^k
-            v[k].r = make_float2(a.x, b.x); v[k].i = make_float2(a.y, b.y);
-        }
-        PDft<16, -1>::run(v);
-        float2 g = __ldg(&TN[low]);                   // W_N^low (odd-bin modulation)
-        if (NEG_B) g = make_float2(-g.x, -g.y);       // ref sits in [L,2L): odd bins change sign
-        const TwPair tw(__ldg(&TN[2 * low]), g);      // W_L^low
-#pragma unroll
-        for (int k = 0; k < 16; k++) s[ppad(low + k * S)] = pc_to(tw.apply(v[k], k));
-    }
+    constexpr int S = Plan<LOG2L>::S1;
+    for (int low = threadIdx.x; low < S; low += kFftThreads)
+        pass1_butterfly<LOG2L, NEG_B>(x, xormask, s, low, __ldg(&TN[2 * low]), __ldg(&TN[low]));
+}
+// one butterfly per thread, twiddle bases already in registers
+template <int LOG2L, bool NEG_B>
+__device__ __forceinline__ void pass1_from_global(const uint8_t *x, uint32_t xormask, float4 *s,
+                                                  float2 w_l, float2 w_n) {
+    if ((int)threadIdx.x < Plan<LOG2L>::S1) pass1_butterfly<LOG2L, NEG_B>(x, xormask, s, threadIdx.x, w_l, w_n);
 }
 
 // ---- in-place mid passes ----------------------------------------------------------------------
-template <int LOG2L, int R, int S, int DIR>
-__device__ __forceinline__ void mid_pass(float4 *s, const float2 *__restrict__ TN) {
+// Every mid pass has at most one butterfly per thread (L <= 8192, 512 threads), so its twiddle base
+// W_(S*R)^low depends on the thread only: mid_twiddle() fetches it once, ahead of the barriers,
+// instead of a dependent global load at the top of each pass.
+template <int LOG2L, int R, int S>
+__device__ __forceinline__ float2 mid_twiddle(const float2 *__restrict__ TN) {
     using P = Plan<LOG2L>;
     constexpr int NB = P::L / R;                      // butterflies
     constexpr int TSTEP = 2 * (P::L / (S * R));       // index step into TN for W_(S*R)
-    for (int bf = threadIdx.x; bf < NB; bf += kFftThreads) {
+    static_assert(NB <= kFftThreads, "one butterfly per thread");
+    const int bf = threadIdx.x < NB ? threadIdx.x : 0;
+    return __ldg(&TN[(bf & (S - 1)) * TSTEP]);
+}
+struct MidTw { float2 a, b; };
+template <int LOG2L>
+__device__ __forceinline__ MidTw mid_twiddles(const float2 *__restrict__ TN) {
+    using P = Plan<LOG2L>;
+    MidTw t; t.a = t.b = make_float2(1.0f, 0.0f);
+    if constexpr (P::RA > 1) t.a = mid_twiddle<LOG2L, P::RA, P::SA>(TN);
+    if constexpr (P::RB > 1) t.b = mid_twiddle<LOG2L, P::RB, 2>(TN);
+    return t;
+}
+
+template <int LOG2L, int R, int S, int DIR>
+__device__ __forceinline__ void mid_pass(float4 *s, float2 w) {
+    using P = Plan<LOG2L>;
+    constexpr int NB = P::L / R;                      // butterflies
+    if (DIR > 0) w = cconj(w);
+    {
+        const int bf = threadIdx.x;
+        if (bf >= NB) return;
         const int low = bf & (S - 1), high = bf / S;
         const int base = high * S * R + low;
-        float2 w = __ldg(&TN[low * TSTEP]);
-        if (DIR > 0) w = cconj(w);
         const TwScalar tw(w);
         PC v[R];
 #pragma unroll
@@ -131,15 +163,19 @@ template <int LOG2L> __device__ __forceinline__ int pair_index(int j) {
 }
 
 template <int LOG2L, int DIR>
-__device__ __forceinline__ void mid_passes(float4 *s, const float2 *TN) {
+__device__ __forceinline__ void mid_passes(float4 *s, const MidTw tw) {
     using P = Plan<LOG2L>;
     if (DIR < 0) {
-        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, -1>(s, TN); mid_sync<LOG2L>(); }
-        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, -1>(s, TN); mid_sync<LOG2L>(); }
+        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, -1>(s, tw.a); mid_sync<LOG2L>(); }
+        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, -1>(s, tw.b); mid_sync<LOG2L>(); }
     } else {
-        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, +1>(s, TN); mid_sync<LOG2L>(); }
-        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, +1>(s, TN); mid_sync<LOG2L>(); }
+        if constexpr (P::RB > 1) { mid_pass<LOG2L, P::RB, 2, +1>(s, tw.b); mid_sync<LOG2L>(); }
+        if constexpr (P::RA > 1) { mid_pass<LOG2L, P::RA, P::SA, +1>(s, tw.a); mid_sync<LOG2L>(); }
     }
+}
+template <int LOG2L, int DIR>
+__device__ __forceinline__ void mid_passes(float4 *s, const float2 *TN) {
+    mid_passes<LOG2L, DIR>(s, mid_twiddles<LOG2L>(TN));
 }
 
 // ---- pair stage --------------------------------------------------------------------------------
@@ -163,19 +199,30 @@ template <int LOG2L>
 __device__ __forceinline__ void pair_correlate(float4 *s, const float4 *__restrict__ R) {
     using P = Plan<LOG2L>;
     constexpr int kTrips = (P::L / 2 + kFftThreads - 1) / kFftThreads;
-    for (int j = 0; j < kTrips; j++) {
-        const int m = pair_index<LOG2L>(j);
-        if (m >= P::L / 2) break;
-        // lanes 0-3 of every quarter-warp touch the even element first, lanes 4-7 the odd one:
-        // the eight 16-byte words of one LDS.128 / STS.128 phase then fall on distinct bank groups
-        const int sw = (threadIdx.x >> 2) & 1;
-        const float4 q0 = s[ppad(2 * m + sw)], q1 = s[ppad(2 * m + 1 - sw)];
-        const PC e0 = pc_from(sw ? q1 : q0), e1 = pc_from(sw ? q0 : q1);
-        const PC r0 = pc_from(__ldg(&R[2 * m])), r1 = pc_from(__ldg(&R[2 * m + 1]));
-        const PC z0 = pc_mulcp(pc_add(e0, e1), r0), z1 = pc_mulcp(pc_sub(e0, e1), r1);
-        const float4 o0 = pc_to(pc_add(z0, z1)), o1 = pc_to(pc_sub(z0, z1));
-        s[ppad(2 * m + sw)] = sw ? o1 : o0;
-        s[ppad(2 * m + 1 - sw)] = sw ? o0 : o1;
+    constexpr int kGroup = kTrips >= 4 ? 4 : kTrips;      // spectrum loads of a whole group in flight
+    // lanes 0-3 of every quarter-warp touch the even element first, lanes 4-7 the odd one:
+    // the eight 16-byte words of one LDS.128 / STS.128 phase then fall on distinct bank groups
+    const int sw = (threadIdx.x >> 2) & 1;
+#pragma unroll 1
+    for (int j0 = 0; j0 < kTrips; j0 += kGroup) {
+        float4 g0[kGroup], g1[kGroup];
+#pragma unroll
+        for (int u = 0; u < kGroup; u++) {
+            const int m = pair_index<LOG2L>(j0 + u);
+            if (j0 + u < kTrips && m < P::L / 2) { g0[u] = __ldg(&R[2 * m]); g1[u] = __ldg(&R[2 * m + 1]); }
+        }
+#pragma unroll
+        for (int u = 0; u < kGroup; u++) {
+            const int m = pair_index<LOG2L>(j0 + u);
+            if (j0 + u >= kTrips || m >= P::L / 2) continue;
+            const float4 q0 = s[ppad(2 * m + sw)], q1 = s[ppad(2 * m + 1 - sw)];
+            const PC e0 = pc_from(sw ? q1 : q0), e1 = pc_from(sw ? q0 : q1);
+            const PC r0 = pc_from(g0[u]), r1 = pc_from(g1[u]);
+            const PC z0 = pc_mulcp(pc_add(e0, e1), r0), z1 = pc_mulcp(pc_sub(e0, e1), r1);
+            const float4 o0 = pc_to(pc_add(z0, z1)), o1 = pc_to(pc_sub(z0, z1));
+            s[ppad(2 * m + sw)] = sw ? o1 : o0;
+            s[ppad(2 * m + 1 - sw)] = sw ? o0 : o1;
+        }
     }
 }
 
