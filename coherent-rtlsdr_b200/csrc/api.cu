@@ -53,7 +53,8 @@ struct cohcuda {
     double prof_ms[3] = { 0, 0, 0 }; uint32_t prof_n[3] = { 0, 0, 0 };
 };
 
-static constexpr uint32_t kCorrChunk = 148;             // blocks per K1/K2 launch: items = 148*C
+static constexpr uint32_t kCorrChunk = 1024;            // blocks per K1/K2 launch (device-resident batches): one spectrum slot of 16 L bytes each;
+                                                        // measured 148 -> 1024: +3 % (fewer launch tails), the spectra then live in HBM not L2
 static constexpr uint32_t kPipeChunk = 74;              // same, when host copies are pipelined around the kernels
 
 #define CK(call)                                                                        \
@@ -162,6 +163,9 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
         if ((e = cudaMemcpy(h->d_TN, tn.data(), sizeof(float2) * h->L, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
     }
     h->corr_chunk = kCorrChunk;
+    if (const char *e = getenv("COHCUDA_CORR_CHUNK")) {              // tuning knob: blocks per K1/K2 launch
+        if (atoi(e) >= 1 && atoi(e) <= 4096) h->corr_chunk = (uint32_t)atoi(e);
+    }
     if (correlate_supported(B) && correlate_is_big(B)) {
         // the split path keeps 16 L bytes of scratch per item in flight: bound it to ~256 items
         uint32_t cc = 256 / cfg->n_signal;
