@@ -224,7 +224,7 @@ def run_reference_arm(args):
                                    f"{cores} DSP threads (one process each) over contiguous block ranges"},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -424,14 +424,35 @@ def run_gpu_arm(args):
                                     "sample": f"{n_cpu} blocks x {nch} channels of the same workload, "
                                               f"{'track' if args.mode == 'mixed' else args.mode} mode, "
                                               f"1 thread (the reference's single DSP thread), {t_cpu:.1f} s"}
-        print(json.dumps(line))
+        emit(line)
     eng.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0
 
 
+_JSON_FD = None
+
+
+def _reserve_stdout():
+    """stdout carries exactly ONE line, the JSON result.  Libraries write there too (NCCL prints its
+    version banner on fd 1 whatever NCCL_DEBUG_FILE says), so fd 1 is pointed at stderr for the whole
+    run and the JSON line goes out through a private duplicate of the original stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
+
 def main():
+    _reserve_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
