@@ -174,6 +174,11 @@ cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st) {
             // alternative schedules of the same transform, kept for comparison (profiles/r1_correlate_history.md)
             const char *e = getenv("COHCUDA_FFT_VARIANT");
             if (e && !strcmp(e, "r8")) return launch_correlate_r8(p, st);
+            if (e && !strcmp(e, "p2")) {
+                CorrLaunch r = p; r.n_items = 0;
+                cudaError_t rc = launch_ref_t<13>(r, st);
+                return rc != cudaSuccess ? rc : launch_correlate_p2(p, st);
+            }
             return launch_ref_t<13>(p, st);
         }
         case 14: case 15: case 16: return launch_correlate_big(p, st);

@@ -28,6 +28,7 @@ struct CorrLaunch {
 };
 cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st);
 cudaError_t launch_correlate_big(const CorrLaunch &p, cudaStream_t st);
+cudaError_t launch_correlate_p2(const CorrLaunch &p, cudaStream_t st);    // L = 8192, two interleaved streams per thread (fft_p2.cu); items only
 cudaError_t launch_correlate_r8(const CorrLaunch &p, cudaStream_t st);    // L = 8192, radix 8 x 1024 threads (fft_r8.cu)
 bool correlate_supported(uint32_t B);
 bool correlate_is_big(uint32_t B);
