@@ -200,3 +200,22 @@ def test_iir_weight_other_than_reference_default(pkg, synth, oracle, alpha):
     np.testing.assert_array_equal(out["phase"].view(np.uint32), ref["phase"].view(np.uint32))
     np.testing.assert_array_equal(out["packets"], ref["packets"])
     eng.close()
+
+
+@pytest.mark.parametrize("variant", ["r8", "p2"])
+def test_alternative_schedules_of_the_8192_point_correlation(pkg, synth, oracle, monkeypatch, variant):
+    """fft_r8.cu / fft_p2.cu: same transform, different schedule (COHCUDA_FFT_VARIANT); kept for
+    comparison, so kept correct.  Integer lag exact, everything downstream byte-identical."""
+    C, B, nb = 5, 16384, 7
+    delays = np.array([0, 17, -250, 4095, -4096])
+    iq, _ = synth.make_blocks(C, B, nb, seed=0xC0DE + 99, delays=delays)
+    monkeypatch.setenv("COHCUDA_FFT_VARIANT", variant)
+    eng = pkg.CoherentCuda(C, B, apply_shift=True)
+    out = eng.batch(iq, lag_mode=pkg.LAG_ALL, readcnt0=8)
+    eng.close()
+    monkeypatch.delenv("COHCUDA_FFT_VARIANT")
+    ref = oracle.process_batch(oracle.make_config(C, B, apply_shift=1, int_dot=1), iq, lag_mode=1, readcnt0=8)
+    assert (out["lag"][:, 1:] == delays[None, :]).all()
+    np.testing.assert_array_equal(out["lag"], ref["lag"])
+    np.testing.assert_allclose(out["mag"], ref["mag"], rtol=1e-4)
+    np.testing.assert_array_equal(out["packets"], ref["packets"])
