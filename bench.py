@@ -301,6 +301,7 @@ def run_gpu_arm(args):
         e0.record(stream)
         for _ in range(steps):
             fn()
+        eng.flush()          # host-buffer steps: the last packet read-back belongs to the timed region
         e1.record(stream)
         barrier()
         return max_over_ranks(e0.elapsed_time(e1))

@@ -25,7 +25,7 @@ LAG_NONE, LAG_ALL = 0, 1
 ABI_SYMBOLS = [
     "cohcuda_create", "cohcuda_destroy", "cohcuda_last_error", "cohcuda_register_host",
     "cohcuda_unregister_host", "cohcuda_packet_layout", "cohcuda_submit_block",
-    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_launch_count",
+    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_flush", "cohcuda_launch_count",
     "cohcuda_device_packets", "cohcuda_get_state", "cohcuda_set_state",
     "cohcuda_cdsp_convtosigned", "cohcuda_cdsp_convtofloat", "cohcuda_cdsp_convto8bit",
     "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
@@ -88,6 +88,7 @@ def load_library():
     L.cohcuda_wait_block.argtypes = [vp, C.POINTER(Result)]
     L.cohcuda_batch.argtypes = [vp, C.POINTER(BatchArgs)]
     L.cohcuda_sync.argtypes = [vp]
+    L.cohcuda_flush.argtypes = [vp]
     L.cohcuda_launch_count.argtypes = [vp]; L.cohcuda_launch_count.restype = C.c_uint64
     L.cohcuda_device_packets.argtypes = [vp]; L.cohcuda_device_packets.restype = vp
     L.cohcuda_get_state.argtypes = [vp, vp, u32]
@@ -163,6 +164,10 @@ class CoherentCuda:
 
     def sync(self):
         self._check(self.lib.cohcuda_sync(self.h), "cohcuda_sync")
+
+    def flush(self):
+        """Stream-ordered join of the packet read-backs into the handle's stream (no host wait)."""
+        self._check(self.lib.cohcuda_flush(self.h), "cohcuda_flush")
 
     def batch(self, iq, lag_mode=LAG_ALL, lag_request=None, refnoise=None, refnoise_enabled=True,
               input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0, cf32_dev=None):

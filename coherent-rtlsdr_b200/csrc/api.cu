@@ -33,6 +33,13 @@ struct cohcuda {
 
     uint32_t cap = 0;                                   // capacity in blocks
     uint8_t *d_iq = nullptr; int8_t *d_packets = nullptr;
+    // second set for host-buffer batches: batch k+1's H2D runs while batch k's packets are still
+    // being read back (the two copy engines stay busy across the batch boundary)
+    uint8_t *d_iq_alt = nullptr; int8_t *d_packets_alt = nullptr;
+    int pp = 0;                                    // set the next host-buffer batch uses
+    uint32_t alt_cap = 0;                          // blocks the second set holds
+    cudaEvent_t ev_comp[2] = {nullptr, nullptr};   // kernels of the last batch that read d_iq[set] are done
+    cudaEvent_t ev_outp[2] = {nullptr, nullptr};   // read-back of the last batch that wrote d_packets[set] is done
     float2 *d_refspec = nullptr; PeakRec *d_peaks = nullptr;
     float *d_lag = nullptr, *d_mag = nullptr; float2 *d_phase = nullptr; uint8_t *d_meas = nullptr;
     uint4 *d_q = nullptr, *d_partial = nullptr;
@@ -74,7 +81,7 @@ template <typename T> static cudaError_t dalloc(T **p, size_t n) {
 template <typename T> static void dfree(T *&p) { if (p) cudaFree(p); p = nullptr; }
 
 static void free_batch_buffers(cohcuda *h) {
-    dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_refspec); dfree(h->d_peaks); dfree(h->d_scratch);
+    dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_iq_alt); dfree(h->d_packets_alt); dfree(h->d_refspec); dfree(h->d_peaks); dfree(h->d_scratch);
     dfree(h->d_lag); dfree(h->d_mag); dfree(h->d_phase); dfree(h->d_meas);
     dfree(h->d_q); dfree(h->d_partial);
     dfree(h->d_src); dfree(h->d_items); dfree(h->d_reflist); dfree(h->d_slot);
@@ -84,11 +91,14 @@ static void free_batch_buffers(cohcuda *h) {
 
 static int ensure_capacity(cohcuda *h, uint32_t nb) {
     if (nb <= h->cap) return COHCUDA_OK;
+    CK(cudaStreamSynchronize(h->s_in));
     CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->s_out));
     free_batch_buffers(h);
     const size_t n = (size_t)nb * h->nch, parts = apply_parts(h->B);
     CK(dalloc(&h->d_iq, n * h->B));
     CK(dalloc(&h->d_packets, (size_t)nb * h->pitch + 16));
+    h->alt_cap = 0;                                  // the second set is allocated by the first host-buffer batch
     if (correlate_supported(h->B)) {
         const uint32_t cc = h->corr_chunk < nb ? h->corr_chunk : nb;       // no more slots than blocks
         CK(dalloc(&h->d_refspec, (size_t)cc * 2 * h->L));
@@ -152,6 +162,10 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
     if ((e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreateWithFlags(&h->ev_out, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    for (int i = 0; i < 2; i++) {
+        if ((e = cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&h->ev_outp[i], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    }
     // twiddle table: exp(-2*pi*i*n/N), n < L, N = 2L, computed in double and rounded once
     {
         std::vector<float2> tn(h->L);
@@ -223,6 +237,7 @@ extern "C" void cohcuda_destroy(cohcuda_t *h) {
     for (auto ev : h->ev_done) cudaEventDestroy(ev);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_out) cudaEventDestroy(h->ev_out);
+    for (int i = 0; i < 2; i++) { if (h->ev_comp[i]) cudaEventDestroy(h->ev_comp[i]); if (h->ev_outp[i]) cudaEventDestroy(h->ev_outp[i]); }
     if (h->pe0) cudaEventDestroy(h->pe0);
     if (h->pe1) cudaEventDestroy(h->pe1);
     if (h->s_in) cudaStreamDestroy(h->s_in);
@@ -264,6 +279,15 @@ extern "C" int cohcuda_sync(cohcuda_t *h) {
     if (!h) return COHCUDA_ERR_ARG;
     CK(cudaStreamSynchronize(h->s_out));
     CK(cudaStreamSynchronize(h->stream));
+    return COHCUDA_OK;
+}
+
+// stream-ordered join: work enqueued on the handle's stream after this call runs after every
+// outstanding packet read-back (no host wait)
+extern "C" int cohcuda_flush(cohcuda_t *h) {
+    if (!h) return COHCUDA_ERR_ARG;
+    CK(cudaEventRecord(h->ev_out, h->s_out));
+    CK(cudaStreamWaitEvent(h->stream, h->ev_out, 0));
     return COHCUDA_OK;
 }
 

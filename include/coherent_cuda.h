@@ -130,9 +130,15 @@ typedef struct {
 
 /* Offline / bench entry: the same per-block schedule over n_blocks consecutive blocks, state
  * carried from block to block exactly as a sequence of submit/wait calls would.  Enqueues on
- * the handle's stream and returns; cohcuda_sync() waits. */
+ * the handle's stream and returns; cohcuda_sync() waits.  With host buffers the copies run on the
+ * library's own copy streams, chunk by chunk around the kernels, and consecutive batches overlap
+ * (the input copies of one with the packet read-back of the previous one): host outputs are complete
+ * after cohcuda_sync(), or -- for work ordered on the handle's stream -- after cohcuda_flush(). */
 int cohcuda_batch(cohcuda_t *h, const cohcuda_batch_args *a);
 int cohcuda_sync(cohcuda_t *h);
+/* stream-ordered join (no host wait): whatever is enqueued on the handle's stream after this call
+ * runs after every packet read-back issued so far */
+int cohcuda_flush(cohcuda_t *h);
 /* kernels launched by this handle so far (bench.py reports it as gpu_launches) */
 uint64_t cohcuda_launch_count(cohcuda_t *h);
 /* per-kernel timing for bench.py's roofline line: while enabled every launch is bracketed by

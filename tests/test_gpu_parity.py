@@ -219,3 +219,31 @@ def test_alternative_schedules_of_the_8192_point_correlation(pkg, synth, oracle,
     np.testing.assert_array_equal(out["lag"], ref["lag"])
     np.testing.assert_allclose(out["mag"], ref["mag"], rtol=1e-4)
     np.testing.assert_array_equal(out["packets"], ref["packets"])
+
+
+def test_back_to_back_host_batches_overlap_safely(pkg, synth):
+    """Host-buffer batches alternate between two device buffer sets so that one batch's input copies
+    overlap the previous batch's packet read-back.  Three batches issued without any wait in between
+    (then one cohcuda_sync) must give the bytes of a single batch over the same blocks."""
+    C, B, nb = 3, 16384, 60
+    iq, _ = synth.make_blocks(C, B, nb, seed=303, delays=np.array([5, -40, 0]))
+    ref_eng = pkg.CoherentCuda(C, B, apply_shift=True)
+    whole = ref_eng.batch(iq, lag_mode=pkg.LAG_ALL, readcnt0=8)
+    ref_eng.close()
+    eng = pkg.CoherentCuda(C, B, apply_shift=True)
+    outs = []
+    for rep in range(2):                                  # second round reuses both buffer sets
+        outs = []
+        for a, b in ((0, 20), (20, 40), (40, 60)):
+            o = {"packets": np.zeros((b - a, eng.packet_len), np.int8), "lag": np.zeros((b - a, C + 1), np.float32),
+                 "part": np.ascontiguousarray(iq[a:b])}
+            eng.batch_raw(iq=o["part"], iq_on_device=0, n_blocks=b - a, lag_mode=pkg.LAG_ALL, refnoise_enabled=1,
+                          readcnt0=8 + a, globalseqn0=a, packets=o["packets"], packets_on_device=0, lag=o["lag"])
+            outs.append(o)
+        eng.sync()
+        if rep == 0:
+            eng.set_state(pkg.CoherentCuda(C, B).get_state())     # fresh channel state for the second round
+    eng.close()
+    got = np.concatenate([o["packets"] for o in outs])
+    np.testing.assert_array_equal(got, whole["packets"])
+    np.testing.assert_array_equal(np.concatenate([o["lag"] for o in outs]), whole["lag"])
