@@ -62,7 +62,8 @@ struct cohcuda {
 
 static constexpr uint32_t kCorrChunk = 1024;            // blocks per K1/K2 launch (device-resident batches): one spectrum slot of 16 L bytes each;
                                                         // measured 148 -> 1024: +3 % (fewer launch tails), the spectra then live in HBM not L2
-static constexpr uint32_t kPipeChunk = 74;              // same, when host copies are pipelined around the kernels
+static constexpr uint32_t kPipeChunk = 148;             // same, when host copies are pipelined around the kernels (swept 24..512 with
+                                                        // batches overlapping: 148 best, 7.99 ms per 1024-block URA21 step)
 
 #define CK(call)                                                                        \
     do {                                                                                \
