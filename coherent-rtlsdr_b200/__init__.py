@@ -25,7 +25,7 @@ LAG_NONE, LAG_ALL = 0, 1
 ABI_SYMBOLS = [
     "cohcuda_create", "cohcuda_destroy", "cohcuda_last_error", "cohcuda_register_host",
     "cohcuda_unregister_host", "cohcuda_packet_layout", "cohcuda_submit_block",
-    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_flush", "cohcuda_launch_count",
+    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_flush", "cohcuda_covariance", "cohcuda_launch_count",
     "cohcuda_device_packets", "cohcuda_get_state", "cohcuda_set_state",
     "cohcuda_cdsp_convtosigned", "cohcuda_cdsp_convtofloat", "cohcuda_cdsp_convto8bit",
     "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
@@ -61,6 +61,20 @@ class BatchArgs(C.Structure):
                 ("mag", C.c_void_p), ("phasecorr", C.c_void_p), ("cf32", C.c_void_p)]
 
 
+def rxx_from_sums(S, m, rows, drop_reference=True, remove_mean=True, scale=1.0 / 128.0):
+    """The clients' covariance estimate from the exact sums of ``covariance_sums``:
+    X = scale * columns (matlabclient/zmqsdr.c:126 scales by 1/128), reference column dropped
+    (heatmap2d2.cpp:189 ``rightCols(cols-1)``), column means removed (heatmap2d2.cpp:190,
+    pmusic.m:13), Rxx = X^H X / rows (heatmap2d2.cpp:199, pmusic.m:14).  sum conj(x_i - mu_i)(x_j - mu_j)
+    = S_ij - conj(m_i) m_j / rows."""
+    S = np.asarray(S, dtype=np.complex128); m = np.asarray(m, dtype=np.complex128)
+    if remove_mean:
+        S = S - np.conj(m)[..., :, None] * m[..., None, :] / rows
+    if drop_reference:
+        S = S[..., 1:, 1:]
+    return (scale * scale / rows) * S
+
+
 class CohCudaError(RuntimeError):
     pass
 
@@ -89,6 +103,7 @@ def load_library():
     L.cohcuda_batch.argtypes = [vp, C.POINTER(BatchArgs)]
     L.cohcuda_sync.argtypes = [vp]
     L.cohcuda_flush.argtypes = [vp]
+    L.cohcuda_covariance.argtypes = [vp, vp, C.c_uint32, vp, vp]
     L.cohcuda_launch_count.argtypes = [vp]; L.cohcuda_launch_count.restype = C.c_uint64
     L.cohcuda_device_packets.argtypes = [vp]; L.cohcuda_device_packets.restype = vp
     L.cohcuda_get_state.argtypes = [vp, vp, u32]
@@ -193,6 +208,20 @@ class CoherentCuda:
                        lag=out["lag"], mag=out["mag"], phasecorr=out["phase"], cf32=cf32_dev)
         self.sync()
         return out
+
+    # ---- downstream: sample covariance of the packet columns ------------------
+    def covariance_sums(self, n_blocks, packets_dev=None):
+        """Exact integer sums over the int8 packet columns of the last batch (or of device packets in
+        the dev_pitch layout): S[b][i][j] = sum conj(x_i) x_j (complex, Hermitian, from int64) and
+        m[b][i] = sum x_i."""
+        n = self.nch
+        S = np.zeros((n_blocks, n, n, 2), dtype=np.int64)
+        m = np.zeros((n_blocks, n, 2), dtype=np.int32)
+        self._check(self.lib.cohcuda_covariance(self.h, packets_dev, n_blocks, _ptr(S), _ptr(m)), "cohcuda_covariance")
+        Sc = S[..., 0] + 1j * S[..., 1]
+        iu = np.triu_indices(n, 1)
+        Sc[:, iu[1], iu[0]] = np.conj(Sc[:, iu[0], iu[1]])          # lower triangle by symmetry
+        return Sc, m[..., 0] + 1j * m[..., 1]
 
     # ---- per-block streaming ------------------------------------------------------------------
     def submit_block(self, chans, readcnt=None, lag_request=None, refnoise_enabled=True,

@@ -292,6 +292,27 @@ extern "C" int cohcuda_flush(cohcuda_t *h) {
     return COHCUDA_OK;
 }
 
+extern "C" int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint32_t n_blocks,
+                                  int64_t *S_host, int32_t *m_host) {
+    if (!h || !S_host || !m_host) { if (h) h->err = "null argument"; return COHCUDA_ERR_ARG; }
+    if (!packets_dev) packets_dev = h->last_packets;
+    if (!packets_dev) { h->err = "no packets: run a batch first or pass device packets"; return COHCUDA_ERR_STATE; }
+    if (n_blocks == 0) return COHCUDA_OK;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->s_out));
+    const size_t nS = (size_t)n_blocks * h->nch * h->nch * 2, nm = (size_t)n_blocks * h->nch * 2;
+    long long *dS = nullptr; int *dm = nullptr;
+    CK(cudaMalloc((void **)&dS, nS * sizeof(long long)));
+    cudaError_t e = cudaMalloc((void **)&dm, nm * sizeof(int));
+    if (e == cudaSuccess) e = launch_covariance(packets_dev, h->pitch, h->lead, h->hdr, h->nch, h->B, n_blocks, dS, dm, h->stream);
+    if (e == cudaSuccess) { h->launches++; e = cudaMemcpyAsync(S_host, dS, nS * sizeof(long long), cudaMemcpyDeviceToHost, h->stream); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(m_host, dm, nm * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dS); cudaFree(dm);
+    CK(e);
+    return COHCUDA_OK;
+}
+
 extern "C" uint64_t cohcuda_launch_count(cohcuda_t *h) { return h ? h->launches : 0; }
 extern "C" const int8_t *cohcuda_device_packets(cohcuda_t *h) { return h ? h->last_packets : nullptr; }
 

@@ -33,6 +33,10 @@ cudaError_t launch_correlate_r8(const CorrLaunch &p, cudaStream_t st);    // L =
 bool correlate_supported(uint32_t B);
 bool correlate_is_big(uint32_t B);
 
+// sample covariance sums of packet columns (cov_kernel.cu); S [blocks][nch][nch][2] int64, m [blocks][nch][2] int32
+cudaError_t launch_covariance(const int8_t *packets, size_t pitch, size_t lead, size_t hdr, uint32_t nch, uint32_t B,
+                              uint32_t n_blocks, long long *S, int *m, cudaStream_t st);
+
 struct ApplyLaunch {
     const uint8_t *iq; uint32_t nch, B, n_blocks;     // n_blocks = whole batch (for the state hand-over)
     uint32_t block0, n_launch_blocks;                  // blocks [block0, block0+n_launch_blocks) in this launch

@@ -149,6 +149,16 @@ int cohcuda_profile_read(cohcuda_t *h, double *ms3, uint32_t *launches3);
 /* device pointer of the internal packet buffer of the last batch (dev_pitch layout) */
 const int8_t *cohcuda_device_packets(cohcuda_t *h);
 
+/* Downstream of the path (no parity target in the reference program itself): the
+ * sums behind the clients' sample covariance Rxx = X^H X / L (beamformclient/heatmap2d2.cpp:199,
+ * matlabclient/functions/pmusic.m:12-14), exact in integers over the int8 packet columns:
+ *   S_host[b][i][j] = sum_n conj(x_i[n]) x_j[n]  as int64 {re, im}, filled for i <= j (Hermitian),
+ *   m_host[b][i]    = sum_n x_i[n]               as int32 {re, im}  (the clients remove the mean).
+ * packets_dev: device packets in the dev_pitch layout, or NULL for the last batch's internal
+ * buffer.  Synchronous. */
+int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint32_t n_blocks,
+                       int64_t *S_host, int32_t *m_host);
+
 /* checkpoint / restore of the per-channel state; n = C+1 entries */
 int cohcuda_get_state(cohcuda_t *h, cohcuda_chan_state *st, uint32_t n);
 int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uint32_t n);

@@ -1,0 +1,12 @@
+import sys, time; sys.path.insert(0, '.')
+import numpy as np, torch, cohpkg
+pkg = cohpkg.load(); synth = cohpkg.synth()
+C, B, nb = 21, 16384, 1024
+iq, _ = synth.make_blocks(C, B, 128, seed=1, delays=np.zeros(C, dtype=int))
+iq = np.ascontiguousarray(np.tile(iq, (8, 1, 1)))
+eng = pkg.CoherentCuda(C, B)
+out = eng.batch(iq, lag_mode=pkg.LAG_NONE)
+for i in range(3):
+    torch.cuda.synchronize(); t0 = time.time(); S, m = eng.covariance_sums(nb); t1 = time.time()
+    print("covariance_sums 1024 blocks incl. alloc + D2H: %.2f ms" % ((t1 - t0) * 1e3))
+eng.close()
