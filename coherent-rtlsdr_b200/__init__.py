@@ -25,7 +25,7 @@ LAG_NONE, LAG_ALL = 0, 1
 ABI_SYMBOLS = [
     "cohcuda_create", "cohcuda_destroy", "cohcuda_last_error", "cohcuda_register_host",
     "cohcuda_unregister_host", "cohcuda_packet_layout", "cohcuda_submit_block",
-    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_flush", "cohcuda_covariance", "cohcuda_launch_count",
+    "cohcuda_wait_block", "cohcuda_batch", "cohcuda_sync", "cohcuda_flush", "cohcuda_covariance", "cohcuda_fraclag", "cohcuda_launch_count",
     "cohcuda_device_packets", "cohcuda_get_state", "cohcuda_set_state",
     "cohcuda_cdsp_convtosigned", "cohcuda_cdsp_convtofloat", "cohcuda_cdsp_convto8bit",
     "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
@@ -104,6 +104,7 @@ def load_library():
     L.cohcuda_sync.argtypes = [vp]
     L.cohcuda_flush.argtypes = [vp]
     L.cohcuda_covariance.argtypes = [vp, vp, C.c_uint32, vp, vp]
+    L.cohcuda_fraclag.argtypes = [vp, vp, C.c_uint32, C.c_int, vp, vp]
     L.cohcuda_launch_count.argtypes = [vp]; L.cohcuda_launch_count.restype = C.c_uint64
     L.cohcuda_device_packets.argtypes = [vp]; L.cohcuda_device_packets.restype = vp
     L.cohcuda_get_state.argtypes = [vp, vp, u32]
@@ -222,6 +223,15 @@ class CoherentCuda:
         iu = np.triu_indices(n, 1)
         Sc[:, iu[1], iu[0]] = np.conj(Sc[:, iu[0], iu[1]])          # lower triangle by symmetry
         return Sc, m[..., 0] + 1j * m[..., 1]
+
+    def fraclag(self, n_blocks, iq_dev=None, input_is_signed=False, want_y3=False):
+        """Fractional delay of every (block, channel) of the last batch (parabola through the exact
+        integer |c|^2 at lag-1, lag, lag+1); total delay = lag + frac."""
+        frac = np.zeros((n_blocks, self.nch), dtype=np.float32)
+        y3 = np.zeros((n_blocks, self.nch, 3), dtype=np.float64) if want_y3 else None
+        self._check(self.lib.cohcuda_fraclag(self.h, iq_dev, n_blocks, int(input_is_signed), _ptr(frac), _ptr(y3)),
+                    "cohcuda_fraclag")
+        return (frac, y3) if want_y3 else frac
 
     # ---- per-block streaming ------------------------------------------------------------------
     def submit_block(self, chans, readcnt=None, lag_request=None, refnoise_enabled=True,

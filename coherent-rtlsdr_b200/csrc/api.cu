@@ -46,6 +46,7 @@ struct cohcuda {
     int32_t *d_src = nullptr; uint32_t *d_items = nullptr, *d_reflist = nullptr, *d_slot = nullptr;
     uint8_t *d_refnoise = nullptr; uint32_t *d_readcnt = nullptr;
     const int8_t *last_packets = nullptr;
+    const uint8_t *last_iq = nullptr; uint32_t last_nb = 0;   // device input and size of the last batch
 
     // pinned staging for the per-block streaming calls
     uint8_t *h_flags = nullptr; uint32_t *h_readcnt = nullptr;
@@ -309,6 +310,26 @@ extern "C" int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint3
     if (e == cudaSuccess) e = cudaMemcpyAsync(m_host, dm, nm * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     cudaFree(dS); cudaFree(dm);
+    CK(e);
+    return COHCUDA_OK;
+}
+
+extern "C" int cohcuda_fraclag(cohcuda_t *h, const uint8_t *iq_dev, uint32_t n_blocks, int input_is_signed,
+                               float *frac_host, double *y3_host) {
+    if (!h || !frac_host) { if (h) h->err = "null argument"; return COHCUDA_ERR_ARG; }
+    if (!iq_dev) iq_dev = h->last_iq;
+    if (!iq_dev || n_blocks > h->last_nb) { h->err = "fraclag: no batch of that size has been run"; return COHCUDA_ERR_STATE; }
+    if (n_blocks == 0) return COHCUDA_OK;
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t n = (size_t)n_blocks * h->nch;
+    float *dF = nullptr; double *dY = nullptr;
+    CK(cudaMalloc((void **)&dF, n * sizeof(float)));
+    cudaError_t e = y3_host ? cudaMalloc((void **)&dY, n * 3 * sizeof(double)) : cudaSuccess;
+    if (e == cudaSuccess) e = launch_fraclag(iq_dev, h->nch, h->B, n_blocks, input_is_signed ? 0u : 0x8080u, h->d_lag, dF, dY, h->stream);
+    if (e == cudaSuccess) { h->launches++; e = cudaMemcpyAsync(frac_host, dF, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream); }
+    if (e == cudaSuccess && y3_host) e = cudaMemcpyAsync(y3_host, dY, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dF); cudaFree(dY);
     CK(e);
     return COHCUDA_OK;
 }

@@ -37,6 +37,10 @@ bool correlate_is_big(uint32_t B);
 cudaError_t launch_covariance(const int8_t *packets, size_t pitch, size_t lead, size_t hdr, uint32_t nch, uint32_t B,
                               uint32_t n_blocks, long long *S, int *m, cudaStream_t st);
 
+// fractional delay by parabolic interpolation of exact integer correlation values (frac_kernel.cu)
+cudaError_t launch_fraclag(const uint8_t *iq, uint32_t nch, uint32_t B, uint32_t n_blocks, uint32_t xormask,
+                           const float *lag, float *frac, double *y3, cudaStream_t st);
+
 struct ApplyLaunch {
     const uint8_t *iq; uint32_t nch, B, n_blocks;     // n_blocks = whole batch (for the state hand-over)
     uint32_t block0, n_launch_blocks;                  // blocks [block0, block0+n_launch_blocks) in this launch

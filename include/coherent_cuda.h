@@ -159,6 +159,16 @@ const int8_t *cohcuda_device_packets(cohcuda_t *h);
 int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint32_t n_blocks,
                        int64_t *S_host, int32_t *m_host);
 
+/* Fractional part of the delay of every (block, channel) of the LAST batch, by three-point
+ * parabolic interpolation of |c|^2 around the integer lag that batch reported -- the estimate
+ * ccoherent::computelag prepares and leaves disabled (src/ccoherent.cc:206-218), with the curvature
+ * sign corrected.  The three correlation values are recomputed exactly in integers in the time
+ * domain.  frac_host: [n_blocks][C+1] (entry 0 = 0), total delay = lag + frac;  y3_host (optional):
+ * [n_blocks][C+1][3] = |c[lag-1]|^2, |c[lag]|^2, |c[lag+1]|^2.  iq_dev: the batch's device input, or
+ * NULL when the batch was given host buffers (the library's staged copy is used).  Synchronous. */
+int cohcuda_fraclag(cohcuda_t *h, const uint8_t *iq_dev, uint32_t n_blocks, int input_is_signed,
+                    float *frac_host, double *y3_host);
+
 /* checkpoint / restore of the per-channel state; n = C+1 entries */
 int cohcuda_get_state(cohcuda_t *h, cohcuda_chan_state *st, uint32_t n);
 int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uint32_t n);
