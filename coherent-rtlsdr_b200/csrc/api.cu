@@ -183,8 +183,10 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
         if (atoi(e) >= 1 && atoi(e) <= 4096) h->corr_chunk = (uint32_t)atoi(e);
     }
     if (correlate_supported(B) && correlate_is_big(B)) {
-        // the split path keeps 16 L bytes of scratch per item in flight: bound it to ~256 items
-        uint32_t cc = 256 / cfg->n_signal;
+        // the split path keeps 16 L bytes of scratch per item in flight: bound the items per launch group
+        uint32_t big_items = 2048;                     // swept 256..5376 at L = 65536: 45.6 -> 52.2 G samples/s (2 GiB of scratch)
+        if (const char *e = getenv("COHCUDA_BIG_ITEMS")) { if (atoi(e) >= 1 && atoi(e) <= 65536) big_items = (uint32_t)atoi(e); }
+        uint32_t cc = big_items / cfg->n_signal;
         h->corr_chunk = cc < 1 ? 1 : (cc > kCorrChunk ? kCorrChunk : cc);
         std::vector<float2> ts(8192);
         for (uint32_t n = 0; n < 8192; n++) {
