@@ -15,7 +15,7 @@
 // of its CTA (no block barrier): lane 0 fetches the channel row -- 16 KiB segment by segment -- into
 // the warp's private shared-memory buffer with ONE bulk asynchronous copy (TMA, cp.async.bulk +
 // mbarrier), the warp forms the dot product from shared memory, looks back, and rotates / packs
-// the same resident bytes (rows longer than a segment are re-fetched, from L2).  Twelve such
+// the same resident bytes (rows longer than a segment are re-fetched, from L2).  Thirteen such
 // warps per SM overlap each other's fetch and look-back latencies, which a CTA-per-item design
 // with block barriers could not (profiles/r1_apply_history.md).  Warps are persistent and draw
 // items through an atomic ticket in (block, channel) order, only when they are ready to start one;
