@@ -7,9 +7,12 @@ One "step" = one pass of the hot path over one batch: URA21 geometry (21 signal 
 channel, 8192-sample blocks, 1024 blocks = BASELINE.json configs[1]).  `value` = coherent samples/s
 ((C+1)*L*blocks / time, every column of the emitted matrix counts) with the input already in HBM;
 `e2e` = the same through cohcuda_batch with pinned HOST buffers (H2D + kernels + D2H timed).
-N > 1 (torchrun): one process per GPU, each rank runs its own shard of blocks with its own copy of
-the reference channel (weak scaling, no data-path collective in `value`); `with_gather` adds the
-NCCL gather of the packed matrix to rank 0.
+N > 1 (torchrun): one process per GPU, each rank runs its own 21 signal channels against its own copy
+of the ONE shared reference channel (weak scaling, no data-path collective in `value`).  `with_gather`
+is BASELINE.json configs[3] when N = 8 (168 = 8 x 21 channels, channel-group sharded): the same step
+through the library's device gather (cohcuda_gather_*, three transports), the gathered
+[hdr][readcnt][1 + 21 N columns] matrix verified byte for byte against a single-GPU engine that
+processes all channels, with the bytes the root received per second.
 `--impl reference` times the reference's CPU path (oracle/_ref when built, else the oracle port)
 on the host cores for the same metric.
 """
@@ -103,16 +106,19 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64):
-    """Synthetic IQ of SURVEY 8d generated on the device (same model as synth.make_blocks)."""
+def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64, ref_seed=None):
+    """Synthetic IQ of SURVEY 8d generated on the device (same model as synth.make_blocks).
+    ref_seed: seed of the reference-noise stream when it is shared by several channel groups
+    (config 4: every rank's 21 channels see the same reference); default = seed."""
     L = blocksize // 2
-    g = torch.Generator(device=device); g.manual_seed(seed)
+    gr = torch.Generator(device=device); gr.manual_seed(seed if ref_seed is None else ref_seed)
+    g = torch.Generator(device=device); g.manual_seed(seed ^ 0x5EED)
     rng = np.random.Generator(np.random.PCG64(seed))
     gains = rng.uniform(0.7, 1.0, n_signal); phases = rng.uniform(-np.pi, np.pi, n_signal)
     delays = rng.integers(-max_delay, max_delay + 1, n_signal)
     pad = max_delay + 1
     T = n_blocks * L + 2 * pad
-    r = torch.randn(T, 2, generator=g, device=device) * 40.0
+    r = torch.randn(T, 2, generator=gr, device=device) * 40.0
     iq = torch.empty(n_blocks, n_signal + 1, blocksize, dtype=torch.uint8, device=device)
 
     def quant(v):
@@ -246,6 +252,112 @@ def bind_to_gpu_numa_node(index):
         pass
 
 
+# ------------------------------------------------------------------------ gather (configs[3])
+def run_with_gather(torch, dist, pkg, eng, iq, args, rank, world, local, dev, stream, timed, barrier, nb, nch, B, L):
+    """The sharded product path: every rank's engine runs its channel group with gather = 1; the
+    library moves the packed columns into the root's [hdr][readcnt][1 + 21 N columns] packets while
+    the next chunk is computed.  Verified against ONE engine that processes all channels."""
+    import ctypes
+    N = 1 + world * C_SIG
+    counts = [C_SIG] * world
+    total_samples = N * L * nb                       # one shared reference column + every rank's 21 columns
+    out = {"config": f"{world} x {C_SIG} = {world * C_SIG} signal channels + 1 shared reference, channel-group sharded, "
+                     f"{nb} blocks of {L} samples; gathered packet = {N} columns",
+           "transports": {}}
+    init_state = eng.get_state()                     # carried state at this point (restored before each verification)
+
+    def reset_state():
+        st = (pkg.ChanState * nch)()
+        for c in range(nch):
+            st[c].phasecorr[0] = st[c].phasecorrprev[0] = 1.0
+        eng.set_state(st)
+
+    def step(mode):
+        eng.batch_raw(iq=iq.data_ptr(), iq_on_device=1, n_blocks=nb, lag_mode=pkg.LAG_ALL if mode == "sync" else pkg.LAG_NONE,
+                      refnoise_enabled=1, gather=1)
+
+    single = None
+    for name in args.gather_transports.split(","):
+        tr = pkg.TRANSPORTS[name]
+        res = {}
+        err = None
+        try:
+            geo = eng.gather_init(rank, world, counts, pkg.SHARD_CHANNELS, tr, max_blocks=nb,
+                                  chunk_blocks=args.gather_chunk, store_ctas=args.store_ctas)
+        except Exception as e:
+            err = f"{type(e).__name__}: {e}"[:300]
+        blob = [None]
+        if rank == 0 and err is None:
+            try:
+                blob = [eng.gather_export()]
+            except Exception as e:
+                err = f"{type(e).__name__}: {e}"[:300]
+        dist.broadcast_object_list(blob, src=0)
+        if err is None and blob[0] is not None:
+            try:
+                eng.gather_attach(blob[0])
+            except Exception as e:
+                err = f"{type(e).__name__}: {e}"[:300]
+        elif err is None:
+            err = "root could not export"
+        # a transport the box cannot do (no peer access, no libnccl) is reported, not fatal -- on every rank alike
+        flag = torch.tensor([0 if err is None else 1], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        if int(flag.item()):
+            errs = [None] * world
+            dist.all_gather_object(errs, err)
+            out["transports"][name] = {"error": next((e for e in errs if e), "failed on another rank")}
+            continue
+        if True:
+            barrier()
+            # ---- verification: fresh state everywhere, one SYNC step, compare with a single engine ------
+            reset_state()
+            step("sync"); eng.sync(); barrier()
+            if rank == 0:
+                if single is None:
+                    big = torch.empty((nb, N, B), dtype=torch.uint8, device=dev)
+                    for g in range(world):
+                        part, _, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * g, dev, ref_seed=0xC0DE + 1)
+                        if g == 0:
+                            big[:, 0, :] = part[:, 0, :]
+                        big[:, 1 + g * C_SIG:1 + (g + 1) * C_SIG, :] = part[:, 1:, :]
+                        del part
+                    e1 = pkg.CoherentCuda(world * C_SIG, B, apply_shift=True, device=local, max_batch_blocks=nb,
+                                          stream=stream.cuda_stream, alpha=args.alpha)
+                    assert (e1.packet_len, e1.dev_pitch, e1.dev_lead) == (geo.packet_len, geo.dev_pitch, geo.dev_lead)
+                    pk1 = torch.zeros(nb * e1.dev_pitch + 16, dtype=torch.int8, device=dev)
+                    e1.batch_raw(iq=big.data_ptr(), iq_on_device=1, n_blocks=nb, lag_mode=pkg.LAG_ALL, refnoise_enabled=1,
+                                 packets=pk1.data_ptr(), packets_on_device=1)
+                    e1.sync(); e1.close(); del big
+                    single = pk1[:nb * e1.dev_pitch].view(nb, e1.dev_pitch)[:, geo.dev_lead:geo.dev_lead + geo.packet_len].cpu().numpy()
+                rows = sorted(set(list(range(0, min(nb, 4))) + list(range(nb // 2, min(nb, nb // 2 + 4))) + list(range(max(nb - 4, 0), nb))))
+                got = np.concatenate([eng.gather_fetch(b, 1) for b in rows])
+                res["verified_blocks"] = len(rows)
+                res["bytes_identical_to_single_gpu"] = bool((got == single[rows]).all())
+                if args.gather_verify_all:
+                    res["all_blocks_identical"] = bool((eng.gather_fetch(0, nb) == single).all())
+            # ---- timing: SYNC and TRACK ---------------------------------------------------------------
+            for mode in ("sync", "track"):
+                b0 = eng.gather_bytes()
+                ms = timed(lambda: step(mode), args.steps, 3)
+                moved = (eng.gather_bytes() - b0) / (args.steps + 3)       # payload per step at this rank
+                t = torch.tensor([float(moved)], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                root_bytes = (world - 1) * C_SIG * B * nb                  # what crosses NVLink into the root per step
+                res[mode] = {"value": total_samples * args.steps / (ms * 1e-3), "unit": "samples/s",
+                             "ms_per_step": ms / args.steps,
+                             "root_ingest_gbs": root_bytes * args.steps / (ms * 1e-3) / 1e9,
+                             "root_ingest_bytes_per_step": root_bytes, "payload_bytes_counted_by_library": int(t.item())}
+        out["transports"][name] = res
+        barrier()
+    eng.set_state(init_state)
+    best = max((r["sync"]["value"] for r in out["transports"].values() if "sync" in r), default=None)
+    out["value"] = best; out["unit"] = "samples/s"
+    out["collective"] = ("gather of the packed int8 columns to rank 0 inside libcoherent_cuda; limit = NVLink ingest of the "
+                         "root (measured peer copy 770 GB/s per direction, B200_PROFILING.md)")
+    return out
+
+
 # ------------------------------------------------------------------------------------ GPU arm
 def run_gpu_arm(args):
     import torch
@@ -267,8 +379,8 @@ def run_gpu_arm(args):
     nb, nch, B, L = args.blocks, C_SIG + 1, BLOCKSIZE, BLOCKSIZE // 2
     eng = pkg.CoherentCuda(C_SIG, B, apply_shift=True, device=local, max_batch_blocks=nb,
                            stream=stream.cuda_stream, alpha=args.alpha)
-    # each rank holds its own shard of blocks and its own copy of the reference channel
-    iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev)
+    # each rank holds its own 21 signal channels and its own copy of the ONE shared reference channel
+    iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev, ref_seed=0xC0DE + 1)
     pk_dev = torch.zeros(nb * eng.dev_pitch + 16, dtype=torch.int8, device=dev)
     torch.cuda.synchronize()
     samples_per_step = nch * L * nb
@@ -373,23 +485,8 @@ def run_gpu_arm(args):
 
     with_gather = None
     if dist is not None:
-        glist = [torch.empty_like(pk_dev) for _ in range(world)] if rank == 0 else None
-
-        def step_gather():
-            step_dev(args.mode)
-            stream.synchronize()
-            dist.gather(pk_dev, glist, dst=0)
-        t0 = time.perf_counter(); barrier()
-        for _ in range(2):
-            step_gather()
-        barrier(); t0 = time.perf_counter()
-        for _ in range(args.steps):
-            step_gather()
-        barrier()
-        ms_g = max_over_ranks((time.perf_counter() - t0) * 1e3)
-        with_gather = {"value": world * samples_per_step * args.steps / (ms_g * 1e-3), "unit": "samples/s",
-                       "collective": "NCCL gather of packed int8 packets to rank 0",
-                       "bytes_per_rank_per_step": int(pk_dev.numel())}
+        with_gather = run_with_gather(torch, dist, pkg, eng, iq, args, rank, world, local, dev, stream,
+                                      timed, barrier, nb, nch, B, L)
 
     if rank == 0:
         val = lambda ms, steps: world * samples_per_step * steps / (ms * 1e-3)
@@ -473,6 +570,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--alpha", type=float, default=0.5, help="phase IIR weight (reference: 0.5)")
     ap.add_argument("--no-refnoise", action="store_true", help="diagnostic: noise source off (no phase estimate)")
+    ap.add_argument("--gather-transports", default="nccl,peer_copy,peer_store")
+    ap.add_argument("--gather-chunk", type=int, default=0, help="blocks per gather transfer (0 = library default)")
+    ap.add_argument("--store-ctas", type=int, default=0, help="CTAs of the NVLink-storing k_apply (0 = library default)")
+    ap.add_argument("--gather-verify-all", action="store_true", help="compare every gathered block, not a sample")
     args = ap.parse_args()
     global C_SIG, BLOCKSIZE, N_BLOCKS, CONFIG, REQ
     CONFIG = args.config

@@ -20,6 +20,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("COHCUDA_LIB") or os.path.join(HERE, "lib", "libcoherent_cuda.so")
 
 LAG_NONE, LAG_ALL = 0, 1
+SHARD_CHANNELS, SHARD_BLOCKS = 0, 1
+GATHER_NCCL, GATHER_PEER_COPY, GATHER_PEER_STORE = 0, 1, 2
+GATHER_BLOB_MAX = 256
+TRANSPORTS = {"nccl": GATHER_NCCL, "peer_copy": GATHER_PEER_COPY, "peer_store": GATHER_PEER_STORE}
 
 # every symbol include/coherent_cuda.h declares
 ABI_SYMBOLS = [
@@ -31,6 +35,9 @@ ABI_SYMBOLS = [
     "cohcuda_cdsp_scalarmul", "cohcuda_cdsp_conj_dotproduct", "cohcuda_cdsp_magsquared",
     "cohcuda_cdsp_conjugatemul", "cohcuda_cdsp_indexofmax", "cohcuda_cdsp_rms",
     "cohcuda_cdsp_fft", "cohcuda_profile", "cohcuda_profile_read",
+    "cohcuda_gather_plan", "cohcuda_gather_init", "cohcuda_gather_export", "cohcuda_gather_attach",
+    "cohcuda_gather_geometry_of", "cohcuda_gather_packets", "cohcuda_gather_fetch", "cohcuda_gather_bytes",
+    "cohcuda_gather_destroy",
 ]
 
 
@@ -58,7 +65,20 @@ class BatchArgs(C.Structure):
                 ("refnoise_enabled", C.c_int), ("input_is_signed", C.c_int),
                 ("readcnt", C.c_void_p), ("readcnt0", C.c_uint32), ("globalseqn0", C.c_uint32),
                 ("packets", C.c_void_p), ("packets_on_device", C.c_int), ("lag", C.c_void_p),
-                ("mag", C.c_void_p), ("phasecorr", C.c_void_p), ("cf32", C.c_void_p)]
+                ("mag", C.c_void_p), ("phasecorr", C.c_void_p), ("cf32", C.c_void_p),
+                ("gather", C.c_int), ("gather_skip_blocks", C.c_uint32), ("sticky_requests", C.c_int)]
+
+
+class GatherConfig(C.Structure):
+    _fields_ = [("rank", C.c_int), ("n_ranks", C.c_int), ("root", C.c_int), ("shard", C.c_int),
+                ("transport", C.c_int), ("rank_count", C.POINTER(C.c_uint32)), ("max_blocks", C.c_uint32),
+                ("chunk_blocks", C.c_uint32), ("store_ctas", C.c_uint32)]
+
+
+class GatherGeometry(C.Structure):
+    _fields_ = [("packet_len", C.c_size_t), ("dev_pitch", C.c_size_t), ("dev_lead", C.c_size_t),
+                ("total_channels", C.c_uint32), ("total_blocks", C.c_uint32), ("first_column", C.c_uint32),
+                ("first_block", C.c_uint32), ("run_offset", C.c_size_t), ("run_bytes", C.c_size_t)]
 
 
 def rxx_from_sums(S, m, rows, drop_reference=True, remove_mean=True, scale=1.0 / 128.0):
@@ -121,6 +141,15 @@ def load_library():
     L.cohcuda_cdsp_fft.argtypes = [vp, vp, vp, i, i, i]
     L.cohcuda_profile.argtypes = [vp, i]
     L.cohcuda_profile_read.argtypes = [vp, vp, vp]
+    L.cohcuda_gather_plan.argtypes = [C.POINTER(GatherConfig), i, u32, i, u32, C.POINTER(GatherGeometry)]
+    L.cohcuda_gather_init.argtypes = [vp, C.POINTER(GatherConfig)]
+    L.cohcuda_gather_export.argtypes = [vp, vp, C.POINTER(C.c_size_t)]
+    L.cohcuda_gather_attach.argtypes = [vp, vp, C.c_size_t]
+    L.cohcuda_gather_geometry_of.argtypes = [vp, C.POINTER(GatherGeometry)]
+    L.cohcuda_gather_packets.argtypes = [vp]; L.cohcuda_gather_packets.restype = vp
+    L.cohcuda_gather_fetch.argtypes = [vp, vp, u32, u32]
+    L.cohcuda_gather_bytes.argtypes = [vp]; L.cohcuda_gather_bytes.restype = C.c_uint64
+    L.cohcuda_gather_destroy.argtypes = [vp]; L.cohcuda_gather_destroy.restype = None
     _lib = L
     return L
 
@@ -186,7 +215,8 @@ class CoherentCuda:
         self._check(self.lib.cohcuda_flush(self.h), "cohcuda_flush")
 
     def batch(self, iq, lag_mode=LAG_ALL, lag_request=None, refnoise=None, refnoise_enabled=True,
-              input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0, cf32_dev=None):
+              input_is_signed=False, readcnt=None, readcnt0=0, globalseqn0=0, cf32_dev=None,
+              gather=False, gather_skip_blocks=0, sticky_requests=False):
         """Host-array convenience: iq uint8 [n_blocks][C+1][B] -> dict of numpy outputs.
         cf32_dev: optional DEVICE pointer (int) receiving the corrected float matrix
         [n_blocks][C+1][L] complex64."""
@@ -194,7 +224,7 @@ class CoherentCuda:
         nb = iq.shape[0]
         assert iq.shape[1:] == (self.nch, self.B), iq.shape
         out = {
-            "packets": np.zeros((nb, self.packet_len), dtype=np.int8),
+            "packets": None if gather else np.zeros((nb, self.packet_len), dtype=np.int8),
             "lag": np.zeros((nb, self.nch), dtype=np.float32),
             "mag": np.zeros((nb, self.nch), dtype=np.float32),
             "phase": np.zeros((nb, self.nch), dtype=np.complex64),
@@ -206,9 +236,41 @@ class CoherentCuda:
                        refnoise=rn, refnoise_enabled=int(refnoise_enabled),
                        input_is_signed=int(input_is_signed), readcnt=rc_, readcnt0=readcnt0,
                        globalseqn0=globalseqn0, packets=out["packets"], packets_on_device=0,
-                       lag=out["lag"], mag=out["mag"], phasecorr=out["phase"], cf32=cf32_dev)
+                       lag=out["lag"], mag=out["mag"], phasecorr=out["phase"], cf32=cf32_dev,
+                       gather=int(bool(gather)), gather_skip_blocks=int(gather_skip_blocks),
+                       sticky_requests=int(bool(sticky_requests)))
         self.sync()
         return out
+
+    # ---- multi-GPU gather (one handle per rank; the blob travels through the caller's plumbing) -----
+    def gather_init(self, rank, n_ranks, rank_count, shard, transport=GATHER_NCCL, max_blocks=1, root=0,
+                    chunk_blocks=0, store_ctas=0):
+        cnt = (C.c_uint32 * n_ranks)(*[int(v) for v in rank_count])
+        cfg = GatherConfig(rank, n_ranks, root, shard, transport, cnt, max_blocks, chunk_blocks, store_ctas)
+        self._check(self.lib.cohcuda_gather_init(self.h, C.byref(cfg)), "cohcuda_gather_init")
+        g = GatherGeometry()
+        self._check(self.lib.cohcuda_gather_geometry_of(self.h, C.byref(g)), "cohcuda_gather_geometry_of")
+        self.gather_geo = g
+        return g
+
+    def gather_export(self):
+        buf = C.create_string_buffer(GATHER_BLOB_MAX); n = C.c_size_t()
+        self._check(self.lib.cohcuda_gather_export(self.h, buf, C.byref(n)), "cohcuda_gather_export")
+        return buf.raw[:n.value]
+
+    def gather_attach(self, blob):
+        self._check(self.lib.cohcuda_gather_attach(self.h, blob, len(blob)), "cohcuda_gather_attach")
+
+    def gather_fetch(self, block0, n_blocks):
+        out = np.zeros((n_blocks, self.gather_geo.packet_len), dtype=np.int8)
+        self._check(self.lib.cohcuda_gather_fetch(self.h, _ptr(out), block0, n_blocks), "cohcuda_gather_fetch")
+        return out
+
+    def gather_bytes(self):
+        return int(self.lib.cohcuda_gather_bytes(self.h))
+
+    def gather_packets_ptr(self):
+        return self.lib.cohcuda_gather_packets(self.h)
 
     # ---- downstream: sample covariance of the packet columns ------------------
     def covariance_sums(self, n_blocks, packets_dev=None):

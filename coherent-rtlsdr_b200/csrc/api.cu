@@ -1,91 +1,16 @@
 // api.cu -- C ABI of libcoherent_cuda (include/coherent_cuda.h): handle, buffers, the batch
 // schedule (K1 ref spectrum -> K2 correlate -> K3 apply) and the per-block streaming calls.
 // Host-side only; kernels live in fft_kernels.cu / apply_kernel.cu / prims.cu.
-#include "coherent_cuda.h"
-#include "kernels.h"
-#include <cmath>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
-
-using namespace coh;
+#include "handle.h"
 
 static std::string g_create_error;
 
-struct cohcuda {
-    cohcuda_config cfg{};
-    uint32_t nch = 0, B = 0, L = 0;
-    size_t hdr = 0, plen = 0, pitch = 0, lead = 0;
-    int sm_count = 0, lookback = 48;
-    cudaStream_t stream = nullptr, s_in = nullptr, s_out = nullptr;
-    bool own_stream = false;
-    std::string err;
-    uint64_t launches = 0;
-
-    float2 *d_TN = nullptr, *d_TN_sub = nullptr;   // W_N^n (n < L) and, for L > 8192, W_16384^n (n < 8192)
-    float4 *d_scratch = nullptr;                   // L > 8192: [corr_chunk * C][L] packed elements (fft_big.cu)
-    uint32_t corr_chunk = 0;                       // blocks per K1/K2 launch group
-    ChanState *d_state[2] = { nullptr, nullptr };
-    int cur = 0;
-    uint32_t *d_ticket = nullptr; uint32_t ticket_total = 0, epoch = 0;
-
-    uint32_t cap = 0;                                   // capacity in blocks
-    uint8_t *d_iq = nullptr; int8_t *d_packets = nullptr;
-    // second set for host-buffer batches: batch k+1's H2D runs while batch k's packets are still
-    // being read back (the two copy engines stay busy across the batch boundary)
-    uint8_t *d_iq_alt = nullptr; int8_t *d_packets_alt = nullptr;
-    int pp = 0;                                    // set the next host-buffer batch uses
-    uint32_t alt_cap = 0;                          // blocks the second set holds
-    cudaEvent_t ev_comp[2] = {nullptr, nullptr};   // kernels of the last batch that read d_iq[set] are done
-    cudaEvent_t ev_outp[2] = {nullptr, nullptr};   // read-back of the last batch that wrote d_packets[set] is done
-    float2 *d_refspec = nullptr; PeakRec *d_peaks = nullptr;
-    float *d_lag = nullptr, *d_mag = nullptr; float2 *d_phase = nullptr; uint8_t *d_meas = nullptr;
-    uint4 *d_q = nullptr, *d_partial = nullptr;
-    int32_t *d_src = nullptr; uint32_t *d_items = nullptr, *d_reflist = nullptr, *d_slot = nullptr;
-    uint8_t *d_refnoise = nullptr; uint32_t *d_readcnt = nullptr;
-    const int8_t *last_packets = nullptr;
-    const uint8_t *last_iq = nullptr; uint32_t last_nb = 0;   // device input and size of the last batch
-
-    // pinned staging for the per-block streaming calls
-    uint8_t *h_flags = nullptr; uint32_t *h_readcnt = nullptr;
-    float *h_lag = nullptr, *h_mag = nullptr, *h_phase = nullptr; uint8_t *h_meas = nullptr;
-    int8_t *h_packet[2] = { nullptr, nullptr };
-    int pk = 0; bool pending = false; uint32_t seq = 0;
-    std::vector<cudaEvent_t> ev_in, ev_done;
-    cudaEvent_t ev_start = nullptr, ev_out = nullptr;
-    std::vector<void *> registered;
-    // optional per-kernel timing (cohcuda_profile): 0 = k_ref_spectrum, 1 = k_correlate, 2 = k_apply
-    bool prof = false; cudaEvent_t pe0 = nullptr, pe1 = nullptr;
-    double prof_ms[3] = { 0, 0, 0 }; uint32_t prof_n[3] = { 0, 0, 0 };
-};
-
-static constexpr uint32_t kCorrChunk = 1024;            // blocks per K1/K2 launch (device-resident batches): one spectrum slot of 16 L bytes each;
-                                                        // measured 148 -> 1024: +3 % (fewer launch tails), the spectra then live in HBM not L2
-static constexpr uint32_t kPipeChunk = 148;             // same, when host copies are pipelined around the kernels (swept 24..512 with
-                                                        // batches overlapping: 148 best, 7.99 ms per 1024-block URA21 step)
-
-#define CK(call)                                                                        \
-    do {                                                                                \
-        cudaError_t e__ = (call);                                                       \
-        if (e__ != cudaSuccess) {                                                       \
-            h->err = std::string(#call) + ": " + cudaGetErrorString(e__);               \
-            return COHCUDA_ERR_CUDA;                                                    \
-        }                                                                               \
-    } while (0)
-
-template <typename T> static cudaError_t dalloc(T **p, size_t n) {
-    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
-    if (e == cudaSuccess) e = cudaMemset(*p, 0, n * sizeof(T));
-    return e;
-}
-template <typename T> static void dfree(T *&p) { if (p) cudaFree(p); p = nullptr; }
+#include "api_gather.inc"
 
 static void free_batch_buffers(cohcuda *h) {
     dfree(h->d_iq); dfree(h->d_packets); dfree(h->d_iq_alt); dfree(h->d_packets_alt); dfree(h->d_refspec); dfree(h->d_peaks); dfree(h->d_scratch);
     dfree(h->d_lag); dfree(h->d_mag); dfree(h->d_phase); dfree(h->d_meas);
-    dfree(h->d_q); dfree(h->d_partial);
+    dfree(h->d_q);
     dfree(h->d_src); dfree(h->d_items); dfree(h->d_reflist); dfree(h->d_slot);
     dfree(h->d_refnoise); dfree(h->d_readcnt);
     h->cap = 0;
@@ -97,7 +22,7 @@ static int ensure_capacity(cohcuda *h, uint32_t nb) {
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->s_out));
     free_batch_buffers(h);
-    const size_t n = (size_t)nb * h->nch, parts = apply_parts(h->B);
+    const size_t n = (size_t)nb * h->nch;
     CK(dalloc(&h->d_iq, n * h->B));
     CK(dalloc(&h->d_packets, (size_t)nb * h->pitch + 16));
     h->alt_cap = 0;                                  // the second set is allocated by the first host-buffer batch
@@ -108,9 +33,9 @@ static int ensure_capacity(cohcuda *h, uint32_t nb) {
     }
     CK(dalloc(&h->d_peaks, n));
     CK(dalloc(&h->d_lag, n)); CK(dalloc(&h->d_mag, n)); CK(dalloc(&h->d_phase, n)); CK(dalloc(&h->d_meas, n));
-    CK(dalloc(&h->d_q, n)); CK(dalloc(&h->d_partial, n * parts));
+    CK(dalloc(&h->d_q, n));
     CK(dalloc(&h->d_src, n)); CK(dalloc(&h->d_items, n)); CK(dalloc(&h->d_reflist, (size_t)nb)); CK(dalloc(&h->d_slot, (size_t)nb));
-    CK(dalloc(&h->d_refnoise, (size_t)nb)); CK(dalloc(&h->d_readcnt, n));
+    CK(dalloc(&h->d_refnoise, (size_t)nb)); CK(dalloc(&h->d_readcnt, n)); h->readcnt_cap = n;
     h->cap = nb;
     return COHCUDA_OK;
 }
@@ -125,7 +50,10 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
         g_create_error = "blocksize must be a power of two >= 64 and n_signal in 1..65535";
         return COHCUDA_ERR_ARG;
     }
-    if (!(cfg->alpha > 0.0f && cfg->alpha <= 1.0f)) { g_create_error = "alpha must be in (0,1]"; return COHCUDA_ERR_ARG; }
+    // the phase IIR is evaluated by a look-back of ceil(48 ln2 / -ln(1-alpha)) blocks, at most 2048:
+    // below alpha = 1 - 2^(-48/2048) the truncated tail would no longer be below fp32 resolution
+    if (!(cfg->alpha >= 0.0162f && cfg->alpha <= 1.0f)) { g_create_error = "alpha must be in [0.0162, 1] (look-back depth <= 2048 blocks)"; return COHCUDA_ERR_ARG; }
+    if (B > (1u << 21)) { g_create_error = "blocksize above 2 MiB is not supported (32-bit lanes of the exact phase dot product)"; return COHCUDA_ERR_ARG; }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) {
@@ -182,6 +110,9 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
     if (const char *e = getenv("COHCUDA_CORR_CHUNK")) {              // tuning knob: blocks per K1/K2 launch
         if (atoi(e) >= 1 && atoi(e) <= 4096) h->corr_chunk = (uint32_t)atoi(e);
     }
+    if (const char *e = getenv("COHCUDA_PIPE_CHUNK")) {              // tuning knob: blocks per pipeline stage of host-buffer batches
+        if (atoi(e) >= 1 && atoi(e) <= (int)kCorrChunk) h->pipe_chunk_env = (uint32_t)atoi(e);
+    }
     if (correlate_supported(B) && correlate_is_big(B)) {
         // the split path keeps 16 L bytes of scratch per item in flight: bound the items per launch group
         uint32_t big_items = 2048;                     // swept 256..5376 at L = 65536: 45.6 -> 52.2 G samples/s (2 GiB of scratch)
@@ -226,6 +157,7 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
 extern "C" void cohcuda_destroy(cohcuda_t *h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
+    cohcuda_gather_destroy(h);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void *p : h->registered) cudaHostUnregister(p);
     free_batch_buffers(h);
@@ -253,7 +185,14 @@ extern "C" void cohcuda_destroy(cohcuda_t *h) {
 extern "C" int cohcuda_register_host(cohcuda_t *h, void *p, size_t bytes) {
     if (!h || !p || !bytes) return COHCUDA_ERR_ARG;
     CK(cudaSetDevice(h->cfg.device));
-    CK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) {
+        // pinning is an optimisation (an unpinned buffer is copied synchronously): report the failure and
+        // clear the runtime's last-error so that the next kernel launch does not inherit it
+        (void)cudaGetLastError();
+        h->err = std::string("cudaHostRegister: ") + cudaGetErrorString(e);
+        return COHCUDA_ERR_CUDA;
+    }
     h->registered.push_back(p);
     return COHCUDA_OK;
 }
@@ -282,6 +221,7 @@ extern "C" int cohcuda_packet_layout(cohcuda_t *h, size_t *packet_len, size_t *d
 extern "C" int cohcuda_sync(cohcuda_t *h) {
     if (!h) return COHCUDA_ERR_ARG;
     CK(cudaStreamSynchronize(h->s_out));
+    if (h->gather) CK(cudaStreamSynchronize(h->gather->s_g));
     CK(cudaStreamSynchronize(h->stream));
     return COHCUDA_OK;
 }
@@ -292,6 +232,10 @@ extern "C" int cohcuda_flush(cohcuda_t *h) {
     if (!h) return COHCUDA_ERR_ARG;
     CK(cudaEventRecord(h->ev_out, h->s_out));
     CK(cudaStreamWaitEvent(h->stream, h->ev_out, 0));
+    if (h->gather) {                                  // and after every transfer of the gather
+        CK(cudaEventRecord(h->gather->ev_join, h->gather->s_g));
+        CK(cudaStreamWaitEvent(h->stream, h->gather->ev_join, 0));
+    }
     return COHCUDA_OK;
 }
 
@@ -368,12 +312,13 @@ extern "C" int cohcuda_set_state(cohcuda_t *h, const cohcuda_chan_state *st, uin
 }
 
 // run one launch, optionally bracketed by events on the launching stream (profile mode syncs)
-template <typename F> static int timed_launch(cohcuda *h, int which, F &&f) {
+template <typename F> static int timed_launch(cohcuda *h, int which, F &&f, cudaStream_t st = nullptr) {
     if (!h->prof) { CK(f()); h->launches++; return COHCUDA_OK; }
+    if (!st) st = h->stream;
     if (!h->pe0) { CK(cudaEventCreate(&h->pe0)); CK(cudaEventCreate(&h->pe1)); }
-    CK(cudaEventRecord(h->pe0, h->stream));
+    CK(cudaEventRecord(h->pe0, st));
     CK(f());
-    CK(cudaEventRecord(h->pe1, h->stream));
+    CK(cudaEventRecord(h->pe1, st));
     CK(cudaEventSynchronize(h->pe1));
     float ms = 0; CK(cudaEventElapsedTime(&ms, h->pe0, h->pe1));
     h->prof_ms[which] += ms; h->prof_n[which]++; h->launches++;

@@ -41,7 +41,10 @@ constexpr int kWarpsPerCta = 13;                          // 13 independent warp
 constexpr int kApplyThreads = 32 * kWarpsPerCta;
 constexpr uint32_t kSegBytes = 16384;                     // shared-memory resident part of a row
 constexpr uint32_t kScratchBytes = 512;                   // look-back scratch: 64 x float2
-constexpr uint32_t kBufBytes = kSegBytes + 32 + kScratchBytes;   // + one chunk of overlap for the shift
+// + one chunk of overlap for the shift; padded to a multiple of 128 B so that every warp's buffer starts on a
+// bank-row boundary (a pitch of 16928 = 32 mod 128 made 12 of 13 warps' LDS.128 bursts straddle five bank rows:
+// 2.67 M load conflicts per step in profiles/r1e_ncu_k_apply.txt)
+constexpr uint32_t kBufBytes = (kSegBytes + 32 + kScratchBytes + 127) / 128 * 128;
 constexpr int kU = 2;                                     // 16-byte chunks per lane per loop trip
 constexpr int kMaxLookback = 2048;
 
@@ -264,7 +267,7 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
     const int nchunks = (int)(B >> 4);
     const int seg_chunks = nchunks < (int)(kSegBytes >> 4) ? nchunks : (int)(kSegBytes >> 4);
     const int nseg = nchunks / seg_chunks;
-    const size_t hdr = p.noheader ? 0 : 16 + 4 * (size_t)nch;
+    const size_t hdr = p.noheader ? 0 : 16 + 4 * (size_t)p.out_nch;
     const float a_w = p.alpha, na_w = 1.0f - p.alpha;
     uint4 *sx = reinterpret_cast<uint4 *>(smem_raw + (size_t)warp * kBufBytes);
     float2 *s_aq = reinterpret_cast<float2 *>(smem_raw + (size_t)warp * kBufBytes + kSegBytes + 32);   // 64 entries
@@ -305,15 +308,16 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
         const size_t bc = (size_t)b * nch + c;
         const uint8_t *xrow = p.iq + bc * B;
         const uint4 *rin = reinterpret_cast<const uint4 *>(p.iq + (size_t)b * nch * B);
-        int8_t *pkt = p.packets + (size_t)b * p.pitch + p.lead;
-        uint4 *col = reinterpret_cast<uint4 *>(pkt + hdr + (size_t)c * B);
+        int8_t *pkt = (b < p.out_skip ? p.packets_skip + (size_t)b * p.pitch
+                                      : p.packets + (size_t)(p.out_block0 + b - p.out_skip) * p.pitch) + p.lead;
+        uint4 *col = reinterpret_cast<uint4 *>(pkt + hdr + (size_t)(c ? p.out_col0 + c - 1 : 0) * B);
 
         if (c == 0) {
             // reference column: raw signed bytes (cpacketize::write(0,..,int8*), cpacketizer.cc:137-156)
-            for (int j = lane; j < nchunks; j += 32) {
+            for (int j = lane; j < nchunks && (p.write_ref || CF); j += 32) {
                 uint4 v = __ldg(rin + j);
                 v.x ^= kToSigned; v.y ^= kToSigned; v.z ^= kToSigned; v.w ^= kToSigned;
-                col[j] = v;
+                if (p.write_ref) col[j] = v;
                 if (CF) {
                     float2 *o = p.cf32 + bc * L + (size_t)j * 8;
                     const uint32_t wv[4] = { v.x, v.y, v.z, v.w };
@@ -326,12 +330,12 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
                     }
                 }
             }
-            if (!p.noheader) {
+            if (!p.noheader && p.write_hdr) {
                 // struct hdr0 (include/cpacketizer.h:32-37) + per-channel readcnt (cpacketizer.cc:142)
                 uint32_t *h32 = reinterpret_cast<uint32_t *>(pkt);
-                if (lane == 0) { h32[0] = p.globalseqn0 + b; h32[1] = nch; h32[2] = L; h32[3] = 0; }
-                for (uint32_t k = lane; k < nch; k += 32)
-                    h32[4 + k] = p.readcnt ? p.readcnt[(size_t)b * nch + k] : p.readcnt0 + b;
+                if (lane == 0) { h32[0] = p.globalseqn0 + b; h32[1] = p.out_nch; h32[2] = L; h32[3] = 0; }
+                for (uint32_t k = lane; k < p.out_nch; k += 32)
+                    h32[4 + k] = p.readcnt ? p.readcnt[(size_t)b * p.out_nch + k] : p.readcnt0 + b;
             }
             if (lane == 0) {
                 if (p.lag) p.lag[bc] = 0.0f;
@@ -474,8 +478,6 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
     if (lane == 0 && item == n_items + total_warps - 1) atomicExch(p.ticket, 0u);
 }
 
-uint32_t apply_parts(uint32_t) { return 1; }
-
 template <bool SIGNED_IN, bool CF>
 static cudaError_t launch_apply_t(const ApplyLaunch &p, uint32_t n_items, cudaStream_t st) {
     const size_t smem = (size_t)kWarpsPerCta * kBufBytes;
@@ -491,7 +493,8 @@ static cudaError_t launch_apply_t(const ApplyLaunch &p, uint32_t n_items, cudaSt
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     uint32_t grid = (n_items + kWarpsPerCta - 1) / kWarpsPerCta;
-    const uint32_t cap = (uint32_t)(p.sm_count > 0 ? p.sm_count : 148) * (uint32_t)occ;
+    uint32_t cap = (uint32_t)(p.sm_count > 0 ? p.sm_count : 148) * (uint32_t)occ;
+    if (p.max_ctas && p.max_ctas < cap) cap = p.max_ctas;
     if (grid > cap) grid = cap;
     k_apply<SIGNED_IN, CF><<<grid, kApplyThreads, smem, st>>>(p, n_items, grid * kWarpsPerCta);
     return cudaGetLastError();

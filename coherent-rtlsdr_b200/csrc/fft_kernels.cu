@@ -20,8 +20,6 @@
 // Forward passes are decimation-in-frequency (natural in, digit-reversed out), inverse passes
 // decimation-in-time (digit-reversed in, natural out), so no reordering pass exists and the
 // reference spectrum is stored in the same digit-reversed order.
-#include <cstdlib>
-#include <cstring>
 #include "fft_passes.cuh"
 
 namespace coh {
@@ -170,17 +168,7 @@ cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st) {
         case 10: return launch_ref_t<10>(p, st);
         case 11: return launch_ref_t<11>(p, st);
         case 12: return launch_ref_t<12>(p, st);
-        case 13: {
-            // alternative schedules of the same transform, kept for comparison (profiles/r1_correlate_history.md)
-            const char *e = getenv("COHCUDA_FFT_VARIANT");
-            if (e && !strcmp(e, "r8")) return launch_correlate_r8(p, st);
-            if (e && !strcmp(e, "p2")) {
-                CorrLaunch r = p; r.n_items = 0;
-                cudaError_t rc = launch_ref_t<13>(r, st);
-                return rc != cudaSuccess ? rc : launch_correlate_p2(p, st);
-            }
-            return launch_ref_t<13>(p, st);
-        }
+        case 13: return launch_ref_t<13>(p, st);
         case 14: case 15: case 16: return launch_correlate_big(p, st);
         default: return cudaErrorInvalidValue;
     }

@@ -25,11 +25,10 @@ struct CorrLaunch {
     // blocks above 8192 samples (fft_big.cu): HBM scratch [n_items][L] float4 and the twiddle
     // table of the 8192-point sub-transforms
     float4 *scratch; const float2 *TN_sub;
+    int sm_count;
 };
 cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st);
 cudaError_t launch_correlate_big(const CorrLaunch &p, cudaStream_t st);
-cudaError_t launch_correlate_p2(const CorrLaunch &p, cudaStream_t st);    // L = 8192, two interleaved streams per thread (fft_p2.cu); items only
-cudaError_t launch_correlate_r8(const CorrLaunch &p, cudaStream_t st);    // L = 8192, radix 8 x 1024 threads (fft_r8.cu)
 bool correlate_supported(uint32_t B);
 bool correlate_is_big(uint32_t B);
 
@@ -55,15 +54,23 @@ struct ApplyLaunch {
     const uint32_t *readcnt; uint32_t readcnt0, globalseqn0;
     const ChanState *state_in; ChanState *state_out;
     int8_t *packets; size_t pitch, lead;                     // device packet layout
+    // where this launch's rows land inside the output packets (multi-GPU gather, api_gather.inc).
+    // Defaults (out_nch = nch, out_col0 = 1, out_block0 = 0, both flags) = one rank's own packets.
+    uint32_t out_nch;               // columns of the output packet: header size 16 + 4*out_nch, hdr0.N
+    uint32_t out_col0;              // output column of local signal channel 1
+    uint32_t out_block0;            // output packet row of local block 0
+    int write_ref, write_hdr;       // this rank writes column 0 / the header + readcnt words
+    uint32_t out_skip;              // local blocks < out_skip (a shard's warm-up halo) are not part of the output:
+    int8_t *packets_skip;           //   their rows go to this local scratch (row b, same pitch/lead) instead
+    uint32_t max_ctas;              // grid cap (0 = one CTA per SM): a k_apply that stores over NVLink runs on a few SMs
     float *lag, *mag; float2 *phase; uint8_t *measured;      // per (block, channel) outputs
     float2 *cf32;                                            // optional corrected float matrix
     // look-back scratch
-    uint4 *q; uint4 *partial; uint32_t epoch;   // 16-byte records {a, b, epoch, check}
-    uint32_t *ticket; uint32_t ticket0;     // device counter and its value at launch
+    uint4 *q; uint32_t epoch;               // 16-byte records {a, b, epoch, check}
+    uint32_t *ticket;                       // device counter (0 between launches)
     int sm_count;
 };
 cudaError_t launch_apply(const ApplyLaunch &p, cudaStream_t st);
-uint32_t apply_parts(uint32_t B);                          // 16 KiB parts per channel-block
 
 // cdsp primitive kernels (device pointers)
 cudaError_t prim_convtosigned(const uint8_t *in, uint8_t *out, int n, cudaStream_t st);

@@ -19,8 +19,14 @@ last measurement (include/csdrdevice.h:138-151).  Two partitionings:
   below fp32 resolution -- the same truncation the CUDA path's decoupled look-back applies
   inside one engine).
 
-The only collective is the gather of the packed int8 packets to rank 0 (``gather_packets``),
-which feeds the reference's unchanged ZMQ publisher; NCCL on GPUs, gloo in the CPU tests.
+The only collective is the gather of the packed int8 packets to rank 0, which feeds the
+reference's unchanged ZMQ publisher.  On GPUs it happens INSIDE libcoherent_cuda
+(``cohcuda_gather_*``, csrc/api_gather.inc): every rank's k_apply writes its columns / rows so that
+they travel chunk by chunk (NCCL send/recv, a copy-engine peer copy, or k_apply's own NVLink stores)
+to their final place in the root's device buffer while the next chunk is computed; this module only
+plans (who owns what) and carries the 136-byte attach blob and the per-block scalars
+(``ShardedCoherent.setup_gather`` / ``run_gathered``).  ``gather_packets`` + ``assemble_*`` are the
+host-side restatement of the same placement, used by the CPU tests (gloo) as the checker.
 
 No arithmetic of the path happens in this file: engines are ``CoherentCuda`` handles (or, in the
 CPU tests only, an injected stand-in with the same ``batch`` signature).
@@ -109,8 +115,9 @@ class ShardedCoherent:
     """One rank's share of a batch.  ``mode`` = "blocks" or "channels"."""
 
     def __init__(self, n_signal, blocksize, rank, world, mode="blocks", alpha=0.5, noheader=False,
-                 apply_shift=False, max_lag_slots=0, engine_factory=None, **engine_kw):
+                 apply_shift=False, max_lag_slots=0, engine_factory=None, transport=None, **engine_kw):
         assert mode in ("blocks", "channels")
+        self.transport = transport          # None: host-side gather (checker); else the library's device gather
         self.C, self.B, self.nch = n_signal, blocksize, n_signal + 1
         self.rank, self.world, self.mode = rank, world, mode
         self.alpha, self.noheader, self.max_lag_slots = alpha, bool(noheader), max_lag_slots
@@ -121,8 +128,10 @@ class ShardedCoherent:
         if mode == "channels":
             self.c0, self.c1 = channel_groups(n_signal, world)[rank]
             n_local = self.c1 - self.c0
-            # columns only: rank 0 assembles header + readcnt + all columns after the gather
-            self.engine = factory(n_local, blocksize, alpha=alpha, noheader=True, apply_shift=apply_shift,
+            # host gather: columns only, rank 0 assembles header + readcnt + all columns afterwards;
+            # device gather: the root's k_apply writes the gathered header itself
+            self.engine = factory(n_local, blocksize, alpha=alpha, noheader=True if transport is None else noheader,
+                                  apply_shift=apply_shift,
                                   max_lag_slots=0, **engine_kw) if n_local > 0 else None
         else:
             self.engine = factory(n_signal, blocksize, alpha=alpha, noheader=noheader, apply_shift=apply_shift,
@@ -181,6 +190,77 @@ class ShardedCoherent:
         k = b0 - h0
         out.update(packets=r["packets"][k:], lag=r["lag"][k:], mag=r["mag"][k:], phase=r["phase"][k:], halo=k,
                    pre_calls=len(pre))
+        return out
+
+
+    # ------------------------------------------------------------------------------------- device gather
+    def setup_gather(self, n_blocks, group=None, chunk_blocks=0, store_ctas=0):
+        """Collective: gather_init on every rank, export on rank 0, the blob through
+        torch.distributed, attach everywhere.  n_blocks = blocks of the whole batch."""
+        import torch.distributed as dist
+        from . import SHARD_BLOCKS, SHARD_CHANNELS, TRANSPORTS
+        assert self.transport in TRANSPORTS, self.transport
+        if self.mode == "channels":
+            counts = [c1 - c0 for c0, c1 in channel_groups(self.C, self.world)]
+            assert min(counts) >= 1, "every rank needs at least one signal channel"
+            shard = SHARD_CHANNELS
+        else:
+            counts = [b1 - b0 for b0, b1 in block_ranges(n_blocks, self.world)]
+            shard = SHARD_BLOCKS
+        self.gather_blocks = n_blocks
+        self.geo = self.engine.gather_init(self.rank, self.world, counts, shard, TRANSPORTS[self.transport],
+                                           max_blocks=max(n_blocks, 1), chunk_blocks=chunk_blocks, store_ctas=store_ctas)
+        blob = [self.engine.gather_export() if self.rank == 0 else None]
+        dist.broadcast_object_list(blob, src=0, group=group)
+        self.engine.gather_attach(blob[0])
+        dist.barrier(group=group)
+
+    def run_gathered(self, iq, lag_request=None, lag_mode=1, refnoise=None, readcnt0=0, globalseqn0=0, group=None,
+                     fetch=True):
+        """Like run() + gather + assembly, but the packets never leave the devices: returns, on rank 0,
+        dict(packets (if fetch), lag, mag, phase) of the whole batch and None elsewhere."""
+        import torch.distributed as dist
+        nb = iq.shape[0]
+        assert nb == self.gather_blocks, "setup_gather() was sized for another batch"
+        req = requests_for_mode(nb, self.nch, lag_mode) if lag_request is None else lag_request
+        req = effective_requests(req, self.max_lag_slots)
+        rn = None if refnoise is None else np.ascontiguousarray(refnoise, dtype=np.uint8)
+        if self.mode == "channels":
+            sel = [0] + list(range(self.c0, self.c1))
+            r = self.engine.batch(np.ascontiguousarray(iq[:, sel, :]), lag_request=np.ascontiguousarray(req[:, sel]),
+                                  refnoise=rn, readcnt0=readcnt0, globalseqn0=globalseqn0, gather=True)
+            small = {"c0": self.c0, "c1": self.c1, "lag": r["lag"][:, 1:], "mag": r["mag"][:, 1:], "phase": r["phase"][:, 1:]}
+        else:
+            b0, b1 = block_ranges(nb, self.world)[self.rank]
+            small = {"b0": b0, "b1": b1}
+            if b1 > b0:
+                pre, h0 = plan_block_shard(req, rn, b0, self.lookback)
+                for blk, flags in pre:                       # restore the held lags as of block h0
+                    self.engine.batch(np.ascontiguousarray(iq[blk:blk + 1]), lag_request=flags[None, :],
+                                      refnoise=np.zeros(1, np.uint8), readcnt0=readcnt0 + blk, globalseqn0=globalseqn0 + blk)
+                r = self.engine.batch(np.ascontiguousarray(iq[h0:b1]), lag_request=np.ascontiguousarray(req[h0:b1]),
+                                      refnoise=None if rn is None else rn[h0:b1], readcnt0=readcnt0 + h0,
+                                      globalseqn0=globalseqn0 + h0, gather=True, gather_skip_blocks=b0 - h0)
+                k = b0 - h0
+                small.update(lag=r["lag"][k:], mag=r["mag"][k:], phase=r["phase"][k:], halo=k, pre_calls=len(pre))
+        # every rank's transfers are complete (batch() synchronised its streams); the barrier makes that
+        # known to the root before it reads the gathered packets
+        dist.barrier(group=group)
+        parts = [None] * self.world if self.rank == 0 else None
+        dist.gather_object(small, parts, dst=0, group=group)
+        if self.rank != 0:
+            return None
+        if self.mode == "channels":
+            lag = np.zeros((nb, self.nch), np.float32); mag = np.zeros((nb, self.nch), np.float32)
+            phase = np.zeros((nb, self.nch), np.complex64); phase[:, 0] = 1.0
+            for p in parts:
+                lag[:, p["c0"]:p["c1"]], mag[:, p["c0"]:p["c1"]], phase[:, p["c0"]:p["c1"]] = p["lag"], p["mag"], p["phase"]
+            out = {"lag": lag, "mag": mag, "phase": phase}
+        else:
+            out = {k: np.concatenate([p[k] for p in parts if "lag" in p], axis=0) for k in ("lag", "mag", "phase")}
+            out["halo"] = np.array([p.get("halo", 0) for p in parts]); out["pre_calls"] = np.array([p.get("pre_calls", 0) for p in parts])
+        if fetch:
+            out["packets"] = self.engine.gather_fetch(0, nb)
         return out
 
 
@@ -253,3 +333,36 @@ def gather_packets(local, dst=0, group=None):
                 raw = bufs[r].cpu().numpy() if bufs[r] is not None else np.zeros(0, np.uint8)
                 parts[r][k] = raw.view(np.dtype(dt)).reshape(shp)
     return parts
+
+
+def gather_by_plan(local_rows, plan_rank, plans, n_blocks, dst=0, group=None, root_head=None):
+    """CPU checker of the library's placement arithmetic: ``plans`` = cohcuda_gather_plan() of every
+    rank (GatherGeometry), ``local_rows`` = this rank's contribution as uint8/int8 [rows][run_bytes]
+    (its columns of every block, or its whole packets).  Rows travel over torch.distributed and are
+    placed at ``run_offset`` of gathered rows ``first_block + i`` -- exactly what api_gather.inc does
+    on the device.  Returns the gathered [total_blocks][packet_len] int8 matrix on ``dst``."""
+    import torch
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    me = plans[plan_rank]
+    local_rows = np.ascontiguousarray(local_rows).view(np.int8)
+    assert local_rows.shape[1] == me.run_bytes, (local_rows.shape, me.run_bytes)
+    shapes = [None] * world
+    dist.all_gather_object(shapes, local_rows.shape, group=group)
+    if rank != dst:
+        if local_rows.size:
+            dist.send(torch.from_numpy(local_rows.reshape(-1).copy()), dst, group=group)
+        return None
+    G = np.zeros((n_blocks, plans[dst].packet_len), np.int8)
+    if root_head is not None:                      # channel shards: the root also writes header, readcnt and column 0
+        G[:, :root_head.shape[1]] = np.ascontiguousarray(root_head).view(np.int8)
+    for r in range(world):
+        rows = local_rows if r == dst else None
+        if r != dst:
+            buf = torch.empty(int(np.prod(shapes[r])), dtype=torch.int8)
+            if buf.numel():
+                dist.recv(buf, r, group=group)
+            rows = buf.numpy().reshape(shapes[r])
+        p = plans[r]
+        G[p.first_block:p.first_block + rows.shape[0], p.run_offset:p.run_offset + p.run_bytes] = rows
+    return G

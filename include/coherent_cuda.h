@@ -126,6 +126,15 @@ typedef struct {
     float         *phasecorr;     /* out, host [n_blocks][C+1][2] or NULL                     */
     float         *cf32;          /* out, DEVICE [n_blocks][C+1][L][2] corrected float matrix
                                      (column 0 = converted ref) or NULL                       */
+    int            gather;        /* 1: this rank's share of a sharded batch -- its packet rows /
+                                     columns go to the root rank's gathered packets (see
+                                     cohcuda_gather_init below); `packets` is ignored           */
+    uint32_t       gather_skip_blocks; /* block shards: leading blocks of this call that are the
+                                     shard's warm-up halo -- computed, not gathered             */
+    int            sticky_requests; /* 1: a lag_request flag stays pending until the channel gets a
+                                     correlation slot, like csdrdevice::lagrequested
+                                     (include/csdrdevice.h:129-151, src/ccoherent.cc:124,266);
+                                     0: flags are the per-block is_lagrequested() state as given */
 } cohcuda_batch_args;
 
 /* Offline / bench entry: the same per-block schedule over n_blocks consecutive blocks, state
@@ -168,6 +177,80 @@ int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint32_t n_block
  * NULL when the batch was given host buffers (the library's staged copy is used).  Synchronous. */
 int cohcuda_fraclag(cohcuda_t *h, const uint8_t *iq_dev, uint32_t n_blocks, int input_is_signed,
                     float *frac_host, double *y3_host);
+
+/* ---- multi-GPU: the gather of the corrected matrix to one rank -------------------
+ * One process and one handle per GPU.  The path shards with no exchange inside the arithmetic;
+ * the only collective is the gather of the packed int8 packets to the rank that feeds the
+ * reference's unchanged publisher (cpacketize::send, src/cpacketizer.cc:109-129).  The gathered
+ * packet is the one packet the reference would have written for ALL channels / blocks:
+ * [hdr0 16][readcnt 4N][N columns x B] (include/cpacketizer.h:32-37, src/cpacketizer.cc:91-96,
+ * 137-172), assembled ON THE DEVICE of the root: every rank's rows land directly at their place.
+ *
+ *   COHCUDA_SHARD_CHANNELS  rank r owns rank_count[r] signal channels for all blocks (its engine is
+ *                           created with n_signal = rank_count[r]); the reference channel is
+ *                           replicated, the root writes column 0, header and readcnt words.
+ *                           readcnt, if given to the root's batch, is [n_blocks][N].
+ *   COHCUDA_SHARD_BLOCKS    rank r owns rank_count[r] consecutive blocks for all channels.
+ *
+ * Transports (all move chunk k while chunk k+1 is being computed):
+ *   COHCUDA_GATHER_NCCL       ncclSend / ncclRecv on a side stream, buffers registered with the
+ *                             communicator; the root places received columns with a strided
+ *                             device copy.  libnccl.so.2 is loaded at run time.
+ *   COHCUDA_GATHER_PEER_COPY  the root's gathered buffer is mapped into every rank (CUDA IPC);
+ *                             each rank's copy engine writes its columns in place over NVLink.
+ *   COHCUDA_GATHER_PEER_STORE same mapping; k_apply itself stores its packed columns through the
+ *                             peer mapping (compute and transfer in one kernel, run on
+ *                             store_ctas SMs beside the next chunk's correlation).
+ * Call order: gather_init on every rank; gather_export on the root; hand the blob to every rank
+ * (torch.distributed / MPI / a socket -- host plumbing, not part of this library); gather_attach
+ * on every rank (collective for NCCL).  Then cohcuda_batch(..., gather = 1) on every rank,
+ * cohcuda_sync(), and a barrier between the ranks before the root reads the packets (for NCCL
+ * the root's own cohcuda_sync() suffices).  Two gathered buffers alternate from batch to batch.
+ */
+#define COHCUDA_SHARD_CHANNELS 0
+#define COHCUDA_SHARD_BLOCKS   1
+#define COHCUDA_GATHER_NCCL       0
+#define COHCUDA_GATHER_PEER_COPY  1
+#define COHCUDA_GATHER_PEER_STORE 2
+#define COHCUDA_GATHER_BLOB_MAX   256
+
+typedef struct {
+    int rank, n_ranks, root;
+    int shard;                    /* COHCUDA_SHARD_*                                            */
+    int transport;                /* COHCUDA_GATHER_*                                           */
+    const uint32_t *rank_count;   /* n_ranks entries: signal channels / blocks of each rank     */
+    uint32_t max_blocks;          /* blocks per gathered batch the buffers must hold            */
+    uint32_t chunk_blocks;        /* blocks per transfer, 0 = default                           */
+    uint32_t store_ctas;          /* PEER_STORE: CTAs of the storing k_apply, 0 = default       */
+} cohcuda_gather_config;
+
+typedef struct {
+    size_t   packet_len;          /* bytes of one gathered packet                               */
+    size_t   dev_pitch, dev_lead; /* device layout of the gathered packets (as packet_layout)   */
+    uint32_t total_channels;      /* N: columns incl. the reference                             */
+    uint32_t total_blocks;        /* rows the gathered buffer holds                             */
+    uint32_t first_column;        /* CHANNELS: gathered column of this rank's signal channel 1  */
+    uint32_t first_block;         /* BLOCKS: gathered row of this rank's first block            */
+    size_t   run_offset;          /* byte offset, from the start of a gathered packet, of the
+                                     contiguous run this rank contributes to each of its rows   */
+    size_t   run_bytes;           /* length of that run                                         */
+} cohcuda_gather_geometry;
+
+/* pure arithmetic (no CUDA call): where rank `rank` of cfg lands in the gathered packets of an
+ * engine with the given blocksize / noheader.  The library uses the same function internally. */
+int cohcuda_gather_plan(const cohcuda_gather_config *cfg, int rank, uint32_t blocksize, int noheader,
+                        uint32_t n_signal_blocks_mode, cohcuda_gather_geometry *out);
+int cohcuda_gather_init(cohcuda_t *h, const cohcuda_gather_config *cfg);
+int cohcuda_gather_export(cohcuda_t *h, void *blob, size_t *blob_len);       /* root only       */
+int cohcuda_gather_attach(cohcuda_t *h, const void *blob, size_t blob_len);
+int cohcuda_gather_geometry_of(cohcuda_t *h, cohcuda_gather_geometry *out);
+/* root: device pointer of the gathered packets written by the last gathered batch             */
+const int8_t *cohcuda_gather_packets(cohcuda_t *h);
+/* root: copies gathered packets [block0, block0 + n_blocks) to host, packet_len pitch; waits  */
+int cohcuda_gather_fetch(cohcuda_t *h, int8_t *host_packets, uint32_t block0, uint32_t n_blocks);
+/* payload bytes this rank has sent to (or, on the root, received from) the other ranks so far */
+uint64_t cohcuda_gather_bytes(cohcuda_t *h);
+void cohcuda_gather_destroy(cohcuda_t *h);
 
 /* checkpoint / restore of the per-channel state; n = C+1 entries */
 int cohcuda_get_state(cohcuda_t *h, cohcuda_chan_state *st, uint32_t n);

@@ -22,7 +22,8 @@ def load_case(name):
 
 
 def test_golden_fixtures_present():
-    assert {"four_cfg", "edge_delay", "mixed_slots", "raw_mode", "track_only"} <= set(CASES)
+    assert {"four_cfg", "edge_delay", "mixed_slots", "raw_mode", "track_only", "dead_channel", "delay_steps",
+            "long_block"} <= set(CASES)
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -46,8 +47,16 @@ def test_golden_known_answers(name):
     assert sent_len == hdr + 2 * (C + 1) * B          # the reference publishes twice the payload (cpacketizer.cc:91-96)
     meas = d["measured"].astype(bool)
     assert meas[:, 1:].sum(axis=1).max() <= nfft - 1   # ccoherent.cc:124 slot cap
-    want = np.broadcast_to(np.concatenate([[0], d["delays"]]).astype(np.float32), d["lag"].shape)
+    want = np.broadcast_to(np.concatenate([[0], d["delays"]]).astype(np.float32), d["lag"].shape).copy()
+    if "delay_matrix" in d.files:                      # delays that step during the run (drift / re-sync)
+        want[:, 1:] = d["delay_matrix"]
+    dead = (d["iq"] == 0x80).all(axis=2)               # a channel that is not streaming: every |c|^2 ties at 0
+    want[dead] = -(B // 2)                             # => first index (volk_32f_index_max_32u), lag = 0 - L
     assert (d["lag"][meas] == want[meas]).all()
+    if dead.any():
+        b, c = np.argwhere(dead)[0]
+        assert np.isnan(d["phase"][b:, c]).all()       # |corr| = 0 => NaN for good (src/csdrdevice.cc:63-67)
+        assert (d["packets"][b:, hdr + c * B:hdr + (c + 1) * B] == 0).all()
     if not noheader:
         h = d["packets"][:, :16].copy().view(np.uint32)
         assert (h[:, 0] == np.arange(nb)).all() and (h[:, 1] == C + 1).all() and (h[:, 2] == B // 2).all()

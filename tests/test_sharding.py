@@ -39,12 +39,12 @@ def make_case(synth, path, C, B, nb, seed, noheader=0, shift=1, slots=0, gated=T
     return iq, req, noise, delays
 
 
-def run_world(mode, case, out, world=2, engine="oracle"):
+def run_world(mode, case, out, world=2, engine="oracle", transport="host", env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(ROOT, "tests", "_shard_worker.py"), "--mode", mode, "--engine", engine,
-           "--case", case, "--out", out]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+           "--case", case, "--out", out, "--transport", transport]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT, env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
 
 
@@ -98,7 +98,9 @@ def test_world2_gloo_gather_equals_single_engine(S, synth, oracle, tmp_path, mod
     C, B, nb = 5, 512, 230
     case, out = str(tmp_path / "case.npz"), str(tmp_path / "out.npz")
     iq, req, noise, _ = make_case(synth, case, C, B, nb, seed=11, noheader=noheader, shift=1, slots=slots)
-    run_world(mode, case, out, world=2)
+    # transport "plan": rank 0 also assembles through cohcuda_gather_plan's geometry (the arithmetic the
+    # device gather uses) and the worker asserts it equals the numpy assembly
+    run_world(mode, case, out, world=2, transport="plan")
     got = np.load(out)
     want = single(oracle, iq, req, noise, C, B, noheader, 1, slots)
     np.testing.assert_array_equal(got["lag"], want["lag"])
@@ -117,3 +119,26 @@ def test_world3_block_shards_with_empty_and_short_ranges(S, synth, oracle, tmp_p
     got = np.load(out)
     want = single(oracle, iq, req, noise, C, B, 0, 1, 0)
     np.testing.assert_array_equal(got["packets"], want["packets"])
+
+
+def test_block_shards_across_a_delay_step(S, synth, oracle, tmp_path):
+    """Drift re-sync over a shard boundary (BASELINE configs[4], src/console.cc:285-289): a delay steps four
+    blocks BEFORE rank 1's range and is re-measured two blocks later (inside rank 1's warm-up halo); another
+    steps inside rank 1's range.  The held lag each rank restores must be the one in force at its halo start."""
+    C, B, nb = 5, 512, 240
+    edge = nb // 2
+    steps = [(edge - 4, 2, 37), (edge + 9, 4, -18), (nb - 30, 1, 3)]
+    iq, _ = synth.make_blocks(C, B, nb, seed=77, delays=np.array([0, 5, -5, 9, 60]), delay_steps=steps)
+    req = np.zeros((nb, C + 1), np.uint8); req[0, 1:] = 1
+    req[edge - 2, 2] = 1; req[edge + 9, 4] = 1; req[nb - 25, 1] = 1
+    noise = np.ones(nb, np.uint8); noise[edge - 20: edge - 12] = 0
+    case, out = str(tmp_path / "case.npz"), str(tmp_path / "out.npz")
+    np.savez(case, iq=iq, lag_request=req, refnoise=noise, meta=np.array([C, B, 0, 1, 0]))
+    run_world("blocks", case, out, world=2, transport="plan")
+    got = np.load(out)
+    want = single(oracle, iq, req, noise, C, B, 0, 1, 0)
+    assert want["lag"][edge, 2] == 37 and want["lag"][edge - 3, 2] == 5     # the step really is in force across the edge
+    np.testing.assert_array_equal(got["lag"], want["lag"])
+    np.testing.assert_array_equal(got["phase"].view(np.uint32), want["phase"].view(np.uint32))
+    np.testing.assert_array_equal(got["packets"], want["packets"])
+    assert got["halo"][1] > 0 and got["pre_calls"][1] >= 1
