@@ -217,6 +217,7 @@ def run_reference_arm(args):
     t, kind = cpu_pass(O, iq, mode, cores, reps=args.steps)
     samples = (C_SIG + 1) * (BLOCKSIZE // 2) * sample_blocks * args.steps
     v = samples / t
+    b3 = cpu_b3(O, iq[:min(sample_blocks, 12)], mode, cores)
     line = {
         "impl": "reference", "metric": "coherent samples/sec", "value": v, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -229,9 +230,27 @@ def run_reference_arm(args):
                          "sample": f"{sample_blocks} blocks x {C_SIG + 1} channels per step, {args.steps} steps, "
                                    f"{cores} DSP threads (one process each) over contiguous block ranges"},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_b3_numpy_scipy": b3,
     }
     emit(line)
     return 0
+
+
+def cpu_b3(O, iq, mode, cores):
+    """the numpy / scipy.fft (pocketfft, complex64) restatement of the same path, timed
+    beside the reference's own translation units, and one 16384-point transform through the shim FFT that
+    stands in for fftw3f against pocketfft -- so that the CPU arm's FFT speed is on the record."""
+    try:
+        nb, nch, B = iq.shape
+        lag_mode = 1 if mode == "sync" else 0
+        O.np_process_batch_c64(iq[:1], lag_mode)
+        t0 = time.perf_counter(); O.np_process_batch_c64(iq, lag_mode, workers=1); t1 = time.perf_counter() - t0
+        t0 = time.perf_counter(); O.np_process_batch_c64(iq, lag_mode, workers=cores); tn = time.perf_counter() - t0
+        n = nch * (B // 2) * nb
+        return {"value_1_thread": n / t1, "value_fft_workers": n / tn, "fft_workers": cores, "unit": "samples/s",
+                "sample": f"{nb} blocks x {nch} channels, {mode} mode", "fft_us_per_16384": O.fft_us(16384)}
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"[:200]}
 
 
 def bind_to_gpu_numa_node(index):
@@ -523,6 +542,7 @@ def run_gpu_arm(args):
             n_cpu = int(min(max(4, 4 * args.cpu_seconds / max(t_probe, 1e-6)), 2048))
             cpu_iq, _ = synth.make_blocks(C_SIG, B, n_cpu, seed=0xC0DE + 1)
             t_cpu, kind = cpu_pass(O, cpu_iq, args.mode, 1)
+            line["cpu_b3_numpy_scipy"] = cpu_b3(O, cpu_iq[:8], "track" if args.mode == "mixed" else args.mode, os.cpu_count() or 1)
             line["cpu_baseline"] = {"value": nch * L * n_cpu / t_cpu, "unit": "samples/s", "cores": 1,
                                     "kind": kind,
                                     "sample": f"{n_cpu} blocks x {nch} channels of the same workload, "

@@ -129,7 +129,7 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
     }
     for (int i = 0; i < 2; i++)
         if ((e = dalloc(&h->d_state[i], (size_t)h->nch)) != cudaSuccess) return fail("cudaMalloc", e);
-    if ((e = dalloc(&h->d_ticket, (size_t)1)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = dalloc(&h->d_ticket, (size_t)4)) != cudaSuccess) return fail("cudaMalloc", e);   // [0] k_apply, [1] k_correlate
     {
         std::vector<ChanState> st(h->nch);
         for (auto &s : st) {            // csdrdevice.cc:36-40

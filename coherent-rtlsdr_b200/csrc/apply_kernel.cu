@@ -34,6 +34,7 @@
 // Arithmetic runs two samples at a time on Blackwell's packed fp32 pipe (FADD2/FMUL2/FFMA2)
 // with the real parts of a word in one register pair and the imaginary parts in the other.
 #include "kernels.h"
+#include "tma.cuh"
 
 namespace coh {
 
@@ -64,23 +65,7 @@ __device__ __forceinline__ uint4 poll16(const uint4 *p, uint32_t epoch) {
     }
 }
 
-// ---- bulk asynchronous copy (TMA) + mbarrier, one barrier per warp ----------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void tma_row_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
+// bulk asynchronous copy (TMA) + mbarrier, one barrier per warp: tma.cuh
 
 // ---- shifted read: x'[n] = x[n + sh] (input domain, zero_code outside the block) --------------
 // The byte offset 16*j + 2*sh has the same residue mod 16 for every 16-byte chunk j, so the

@@ -26,6 +26,7 @@ struct CorrLaunch {
     // table of the 8192-point sub-transforms
     float4 *scratch; const float2 *TN_sub;
     int sm_count;
+    uint32_t *ticket;               // device counter of the persistent L = 8192 kernel (NULL: one CTA per item)
 };
 cudaError_t launch_correlate(const CorrLaunch &p, cudaStream_t st);
 cudaError_t launch_correlate_big(const CorrLaunch &p, cudaStream_t st);

@@ -46,6 +46,10 @@ struct Engine {
     std::vector<const void *> pinned;           // librtlsdr buffers already registered
     cohcuda_result res{};                       // result of the block in flight
     bool have_result = false;
+    // which device sat in which engine channel, and whether it streamed, in the previous block: when that
+    // changes (a dongle starts or stops, console add / del) the engine's per-channel state no longer
+    // belongs to the device in that slot and is re-seeded from the devices' own phasecorr / phasecorrprev
+    std::vector<std::pair<const void *, uint8_t>> slots;
 };
 
 std::map<const ccoherent *, Engine *> g_engines;
@@ -223,16 +227,38 @@ void ccoherent::threadf(ccoherent *ctx)
             k++;
         }
         if (ctx->devices->size() == 0) { e->chan[1] = e->chan[0]; e->request[1] = 0; e->ready[1] = 0; }
+        {
+            // csdrdevice::phasecorr is the truth (include/csdrdevice.h:74-76; a skipped device keeps it untouched,
+            // src/ccoherent.cc:264): the engine's copy follows it whenever the slot assignment changed
+            std::vector<std::pair<const void *, uint8_t>> now;
+            uint32_t j = 1;
+            for (auto *d : *ctx->devices) { now.emplace_back((const void *)d, e->ready[j]); j++; }
+            if (now != e->slots) {
+                std::vector<cohcuda_chan_state> st(e->n_signal + 1);
+                if (cohcuda_get_state(e->h, st.data(), e->n_signal + 1) != COHCUDA_OK) die("cohcuda_get_state", e->h);
+                j = 1;
+                for (auto *d : *ctx->devices) {
+                    if (j > e->n_signal) break;
+                    st[j].phasecorr[0] = d->phasecorr.real(); st[j].phasecorr[1] = d->phasecorr.imag();
+                    st[j].phasecorrprev[0] = d->phasecorrprev.real(); st[j].phasecorrprev[1] = d->phasecorrprev.imag();
+                    j++;
+                }
+                if (cohcuda_set_state(e->h, st.data(), e->n_signal + 1) != COHCUDA_OK) die("cohcuda_set_state", e->h);
+                e->slots = now;
+            }
+        }
 
-        // buffers were XORed to two's complement by cbuffer::setbufferptr (include/common.h:121)
+        // cbuffer::setbufferptr's in-place XOR (include/common.h:121) is deferred to the kernels' load path
+        // (host/cdsp.cc): the buffers are still offset-binary unless COHCUDA_HOST_XOR_ON_CALL=1
+        const int deferred = cohcuda_host_xor_deferred();
         if (cohcuda_submit_block(e->h, e->chan.data(), e->readcnt.data(), e->request.data(),
-                                 ctx->refnoise->isenabled() ? 1 : 0, /*input_is_signed=*/1) != COHCUDA_OK)
+                                 ctx->refnoise->isenabled() ? 1 : 0, /*input_is_signed=*/deferred ? 0 : 1) != COHCUDA_OK)
             die("cohcuda_submit_block", e->h);
         if (cohcuda_wait_block(e->h, &e->res) != COHCUDA_OK) die("cohcuda_wait_block", e->h);
         e->have_result = true;
 
-        // reference column: raw signed bytes (:254-255)
-        ctx->refdev->packetize.write(0, e->readcnt[0], refsptr);
+        // reference column: raw signed bytes (:254-255) -- the library's column 0 when the XOR was deferred
+        ctx->refdev->packetize.write(0, e->readcnt[0], deferred ? const_cast<int8_t *>(e->res.packet) : refsptr);
         ctx->refdev->consume();
 
         int c = 1; k = 1;

@@ -74,8 +74,23 @@ extern "C" void cohcuda_host_destroy_fft_scheme(void *scheme) { delete (cohcuda_
 #define H cohcuda_host_prim_handle()
 
 // src/cdsp.cc:21-34 (n bytes, multiple of 8; `out` is written despite its const qualifier)
+//
+// The one hot caller is cbuffer::setbufferptr (include/common.h:121): every librtlsdr callback thread
+// converts its 16 KiB USB buffer IN PLACE, 250 times a second per dongle.  Routing that through the GPU
+// would be a synchronised H2D + kernel + D2H round trip under one mutex per USB buffer (5500 per second
+// for URA21).  The drop-in therefore DEFERS the in-place form: the bytes stay offset-binary, the DSP
+// thread hands them to cohcuda_submit_block with input_is_signed = 0 and every kernel applies ^0x80 in
+// its load; column 0 of the packet is then taken from the library's packet, not from the
+// raw buffer.  Out-of-place calls (a caller that wants the converted bytes) still run the kernel.
+// COHCUDA_HOST_XOR_ON_CALL=1 restores the convert-at-call behaviour for in-place calls too.
+extern "C" int cohcuda_host_xor_deferred(void)
+{
+    static const int deferred = [] { const char *e = std::getenv("COHCUDA_HOST_XOR_ON_CALL"); return (e && std::atoi(e)) ? 0 : 1; }();
+    return deferred;
+}
 void cdsp::convtosigned(const uint8_t *in, const uint8_t *out, int n)
 {
+    if (in == out && cohcuda_host_xor_deferred()) return;
     PRIM(cohcuda_cdsp_convtosigned(H, in, const_cast<uint8_t *>(out), n));
 }
 

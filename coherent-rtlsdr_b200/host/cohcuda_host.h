@@ -14,6 +14,10 @@ cohcuda_t *cohcuda_host_prim_handle(void);
  * (src/ccoherent.cc:87-93): the object an fft_scheme must point to for cdsp::fft on this path */
 void *cohcuda_host_make_fft_scheme(int n, int howmany, int sign, void *in, void *out);
 void cohcuda_host_destroy_fft_scheme(void *scheme);
+/* 1 (default): cdsp::convtosigned's in-place form -- the XOR cbuffer::setbufferptr asks for in the USB
+ * callback thread (include/common.h:121) -- is deferred to the kernels' load path; the DSP thread then
+ * submits offset-binary buffers with input_is_signed = 0.  0 when COHCUDA_HOST_XOR_ON_CALL=1. */
+int cohcuda_host_xor_deferred(void);
 /* the engine a ccoherent instance drives (NULL if none is alive); for status displays/tests */
 cohcuda_t *cohcuda_host_engine(const void *ccoherent_instance);
 #ifdef __cplusplus

@@ -152,6 +152,60 @@ def np_pack8(v):
     return np.rint(r).astype(np.int8)
 
 
+def np_process_batch_c64(iq, lag_mode=1, alpha=0.5, workers=1):
+    """the whole per-block path in numpy / scipy.fft complex64 (pocketfft), vectorised
+    over the channels of a block -- reference layout (crtlsdr.cc:205-218), fft -> conjugatemul -> ifft ->
+    magsquared -> indexofmax (ccoherent.cc:174-192), conjugate dot + IIR (csdrdevice.cc:58-69), scalarmul
+    (:80-84), convto8bit (cpacketizer.cc:158-172).  A cross-check and a timed CPU baseline, never the
+    checker of record (that is the C port held bit-for-bit to the reference's golden vectors)."""
+    import scipy.fft as sf
+    nb, nch, B = iq.shape
+    L = B // 2
+    lag = np.zeros((nb, nch), np.float32); mag = np.zeros((nb, nch), np.float32)
+    pk = np.empty((nb, nch, B), np.int8)
+    p = np.ones(nch - 1, np.complex64)
+    a, na = np.float32(alpha), np.float32(1.0 - alpha)
+    buf = np.zeros((nch, 2 * L), np.complex64)
+    for b in range(nb):
+        f = np_to_complex(np_convtofloat(iq[b]))                      # [nch][L] complex64
+        if lag_mode:
+            buf[0, :L] = 0; buf[0, L:] = f[0]                         # ref in the second half (crtlsdr.cc:215-218)
+            buf[1:, :L] = f[1:]; buf[1:, L:] = 0
+            S = sf.fft(buf, axis=1, workers=workers)
+            c = sf.ifft(S[1:] * np.conj(S[0]), axis=1, norm="forward", workers=workers)
+            m = c.real * c.real + c.imag * c.imag
+            idx = np.argmax(m, axis=1)
+            lag[b, 1:] = idx.astype(np.float32) - np.float32(L)
+            mag[b, 1:] = np.sqrt(m[np.arange(nch - 1), idx] / np.float32(L))
+        corr = (f[1:] * np.conj(f[0])).sum(axis=1, dtype=np.complex64)
+        q = np.conj(corr) * (np.float32(1.0) / np.abs(corr))
+        p = (a * q + na * p).astype(np.complex64)
+        y = f[1:] * p[:, None]
+        pk[b, 0] = (iq[b, 0] ^ np.uint8(0x80)).view(np.int8)
+        pk[b, 1:] = np_pack8(y.view(np.float32).reshape(nch - 1, B))
+    return {"packets": pk, "lag": lag, "mag": mag, "phase": p}
+
+
+def fft_us(n=16384, reps=200):
+    """micro-timing printed beside the CPU arms: one n-point complex64 forward transform, 1 thread, through
+    (a) the shim FFT that stands in for fftw3f inside oracle/_ref and the C port, (b) scipy's pocketfft."""
+    import time
+    import scipy.fft as sf
+    rng = np.random.default_rng(0)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    y = np.empty_like(x)
+    lib().orc_fft(_p(y), _p(x), n, -1); sf.fft(x)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        lib().orc_fft(_p(y), _p(x), n, -1)
+    t_shim = (time.perf_counter() - t0) / reps
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        sf.fft(x)
+    t_pf = (time.perf_counter() - t0) / reps
+    return {"n": n, "shim_fft_us": t_shim * 1e6, "pocketfft_us": t_pf * 1e6}
+
+
 # ------------------------------------------------- the reference's own TUs (oracle/_ref) -----
 # libref_cdsp.so = /root/reference's cdsp.cc, ccoherent.cc, csdrdevice.cc, crtlsdr.cc,
 # cpacketizer.cc, common.cc, ccontrol.cc compiled unmodified against oracle/shim/ plus
