@@ -66,7 +66,7 @@ def measured_peaks():
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw")
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
@@ -102,8 +102,15 @@ class ClockSampler:
         mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        pw = []
+        for r in self.rows:
+            try:
+                pw.append(float(r[6]))
+            except Exception:
+                pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "sm_mhz_min": min(sm) if sm else None,
+                "power_w_max": max(pw) if pw else None}
 
 
 def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64, ref_seed=None):
@@ -502,6 +509,20 @@ def run_gpu_arm(args):
     e2e_steps = max(args.steps // 2, 2)
     lag_ok = bool((h_lag[:, 1:].numpy() == delays[None, :]).all()) if args.mode == "sync" else None
 
+    # ---- sustained run (BASELINE configs[4] is "sustained throughput"): seconds, not a 50 ms burst ----------
+    sustained = None
+    if args.sustained > 0:
+        sustained = {}
+        for m, mult in ((args.mode, 1), (other, 1)):
+            n_steps = int(args.sustained * (12 if m == "track" else 1))
+            smp = ClockSampler(local)
+            if rank == 0:
+                smp.start()
+            ms = timed(lambda: step_dev(m), n_steps, 3)
+            ck = smp.stop() if rank == 0 else None
+            sustained[m] = {"steps": n_steps, "seconds": ms * 1e-3, "value": world * samples_per_step * n_steps / (ms * 1e-3),
+                            "unit": "samples/s", "clocks": ck}
+
     with_gather = None
     if dist is not None:
         with_gather = run_with_gather(torch, dist, pkg, eng, iq, args, rank, world, local, dev, stream,
@@ -534,6 +555,8 @@ def run_gpu_arm(args):
         }
         if with_gather:
             line["with_gather"] = with_gather
+        if sustained:
+            line["sustained"] = sustained
         if world == 1 and not args.no_cpu:
             from oracle import oracle as O
             synth = cohpkg.synth()
@@ -590,6 +613,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--alpha", type=float, default=0.5, help="phase IIR weight (reference: 0.5)")
     ap.add_argument("--no-refnoise", action="store_true", help="diagnostic: noise source off (no phase estimate)")
+    ap.add_argument("--sustained", type=int, default=0, help="also time this many back-to-back SYNC steps (12x as many TRACK steps) with the clock / power record")
     ap.add_argument("--gather-transports", default="nccl,peer_copy,peer_store")
     ap.add_argument("--gather-chunk", type=int, default=0, help="blocks per gather transfer (0 = library default)")
     ap.add_argument("--store-ctas", type=int, default=0, help="CTAs of the NVLink-storing k_apply (0 = library default)")

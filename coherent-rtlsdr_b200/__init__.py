@@ -141,6 +141,9 @@ def load_library():
     L.cohcuda_cdsp_fft.argtypes = [vp, vp, vp, i, i, i]
     L.cohcuda_profile.argtypes = [vp, i]
     L.cohcuda_profile_read.argtypes = [vp, vp, vp]
+    if not hasattr(L, "cohcuda_gather_plan"):        # an older build of the library (kernel A/B experiments via COHCUDA_LIB)
+        _lib = L
+        return L
     L.cohcuda_gather_plan.argtypes = [C.POINTER(GatherConfig), i, u32, i, u32, C.POINTER(GatherGeometry)]
     L.cohcuda_gather_init.argtypes = [vp, C.POINTER(GatherConfig)]
     L.cohcuda_gather_export.argtypes = [vp, vp, C.POINTER(C.c_size_t)]

@@ -45,7 +45,10 @@ constexpr uint32_t kScratchBytes = 512;                   // look-back scratch: 
 // + one chunk of overlap for the shift; padded to a multiple of 128 B so that every warp's buffer starts on a
 // bank-row boundary (a pitch of 16928 = 32 mod 128 made 12 of 13 warps' LDS.128 bursts straddle five bank rows:
 // 2.67 M load conflicts per step in profiles/r1e_ncu_k_apply.txt)
-constexpr uint32_t kBufBytes = (kSegBytes + 32 + kScratchBytes + 127) / 128 * 128;
+#ifndef COH_APPLY_PAD
+#define COH_APPLY_PAD 128
+#endif
+constexpr uint32_t kBufBytes = (kSegBytes + 32 + kScratchBytes + COH_APPLY_PAD - 1) / COH_APPLY_PAD * COH_APPLY_PAD;
 constexpr int kU = 2;                                     // 16-byte chunks per lane per loop trip
 constexpr int kMaxLookback = 2048;
 
@@ -299,19 +302,30 @@ k_apply(const ApplyLaunch p, uint32_t n_items, uint32_t total_warps) {
 
         if (c == 0) {
             // reference column: raw signed bytes (cpacketize::write(0,..,int8*), cpacketizer.cc:137-156)
-            for (int j = lane; j < nchunks && (p.write_ref || CF); j += 32) {
-                uint4 v = __ldg(rin + j);
-                v.x ^= kToSigned; v.y ^= kToSigned; v.z ^= kToSigned; v.w ^= kToSigned;
-                if (p.write_ref) col[j] = v;
-                if (CF) {
-                    float2 *o = p.cf32 + bc * L + (size_t)j * 8;
-                    const uint32_t wv[4] = { v.x, v.y, v.z, v.w };
-                    const float cc = 0x1.020408p-7f;
+            if (p.write_ref || CF) {
+                // four independent 16-byte loads in flight per lane (a serial copy of the 16 KiB row would hold
+                // this warp for ~30 us of load latency)
+                for (int j0 = lane; j0 < nchunks; j0 += 128) {
+                    uint4 v[4];
 #pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        int w = (int)wv[k];
-                        o[2 * k] = make_float2(__fmul_rn((float)(signed char)(w & 0xff), cc), __fmul_rn((float)(signed char)((w >> 8) & 0xff), cc));
-                        o[2 * k + 1] = make_float2(__fmul_rn((float)(signed char)((w >> 16) & 0xff), cc), __fmul_rn((float)(signed char)((w >> 24) & 0xff), cc));
+                    for (int u = 0; u < 4; u++) if (j0 + 32 * u < nchunks) v[u] = __ldg(rin + j0 + 32 * u);
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int j = j0 + 32 * u;
+                        if (j >= nchunks) break;
+                        v[u].x ^= kToSigned; v[u].y ^= kToSigned; v[u].z ^= kToSigned; v[u].w ^= kToSigned;
+                        if (p.write_ref) col[j] = v[u];
+                        if (CF) {
+                            float2 *o = p.cf32 + bc * L + (size_t)j * 8;
+                            const uint32_t wv[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
+                            const float cc = 0x1.020408p-7f;
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                int w = (int)wv[k];
+                                o[2 * k] = make_float2(__fmul_rn((float)(signed char)(w & 0xff), cc), __fmul_rn((float)(signed char)((w >> 8) & 0xff), cc));
+                                o[2 * k + 1] = make_float2(__fmul_rn((float)(signed char)((w >> 16) & 0xff), cc), __fmul_rn((float)(signed char)((w >> 24) & 0xff), cc));
+                            }
+                        }
                     }
                 }
             }

@@ -47,7 +47,7 @@ k_ref_spectrum(const uint8_t *__restrict__ iq, size_t block_stride, const uint32
 // last inverse pass (radix 16, stride L/16) kept in registers; recombine the halves,
 // |.|^2 (cdsp::magsquared, src/cdsp.cc:100-103) and running arg-max with lowest-index ties
 // (volk_32f_index_max_32u semantics, src/cdsp.cc:135-139)
-template <int LOG2L>
+template <int LOG2L, int PADSH = 4>
 __device__ __forceinline__ void last_pass_argmax(const float4 *smem4, float2 w_l, float2 w_n, float &best, uint32_t &bidx) {
     using P = Plan<LOG2L>;
     constexpr int L = P::L, S = P::S1;
@@ -56,7 +56,7 @@ __device__ __forceinline__ void last_pass_argmax(const float4 *smem4, float2 w_l
         {
             const TwPair tw(cconj(w_l), cconj(w_n));
 #pragma unroll
-            for (int k = 0; k < 16; k++) v[k] = tw.apply(pc_from(smem4[ppad(low + k * S)]), k);
+            for (int k = 0; k < 16; k++) v[k] = tw.apply(pc_from(smem4[ppad_t<PADSH>(low + k * S)]), k);
         }
         PDft<16, +1>::run(v);
         float2 mg[16];                                 // (|c[m]|^2, |c[m+L]|^2), m = low + k*S
@@ -160,12 +160,31 @@ k_correlate(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, const uint
 // pass-1 writes touch the SAME sixteen slots {low + k L/16}, so the last pass of item i-1 and pass 1 of
 // item i run back to back in one phase (X) with no barrier between them:
 //     X(i): last pass + arg-max of item i-1, then pass 1 of item i      -- barrier
-//     M(i): forward mid passes, x conj(R), inverse mid passes (warp local) -- barrier
+//     M(i): forward mid pass, fused 32-point stage with x conj(R), inverse mid pass (warp local) -- barrier
 // The CTA never drains between items (no launch gap, no cold start on pass 1's loads, two block barriers
 // per item instead of three), and the raw bytes of item i+1 arrive by ONE bulk asynchronous copy (TMA,
 // cp.async.bulk + mbarrier) into a 16 KiB staging buffer while item i is transformed -- pass 1 reads
 // them with LDS instead of sixteen 2-byte global loads per thread.
 struct ItemMeta { uint32_t b, c, slot, valid; };
+constexpr size_t kPersistSmemData = ((size_t)ppadded_len_t<5>(8192) * sizeof(float4) + 127) / 128 * 128;
+
+// reference spectrum in the register order of the fused 32-point stage (fft_passes.cuh, fused_b_out)
+template <int LOG2L>
+__global__ void __launch_bounds__(kFftThreads, 1)
+k_ref_spectrum_fused(const uint8_t *__restrict__ iq, size_t block_stride, const uint32_t *__restrict__ block_list,
+                     uint32_t xormask, const float2 *__restrict__ TN, float4 *__restrict__ refspec) {
+    using P = Plan<LOG2L>;
+    extern __shared__ __align__(16) float4 smem4[];
+    const uint32_t slot = blockIdx.x;
+    const uint32_t b = block_list ? block_list[slot] : slot;
+    const uint8_t *x = iq + (size_t)b * block_stride;          // channel 0 of block b
+    const float2 w_a = mid_twiddle<LOG2L, P::RA, P::SA>(TN);
+    pass1_butterfly<LOG2L, true, 5>(x, xormask, smem4, threadIdx.x, __ldg(&TN[2 * threadIdx.x]), __ldg(&TN[threadIdx.x]));
+    __syncthreads();
+    mid_pass<LOG2L, P::RA, P::SA, -1, 5>(smem4, w_a);
+    __syncwarp();
+    fused_b_out<LOG2L>(smem4, refspec + (size_t)slot * P::L);
+}
 
 template <int LOG2L>
 __global__ void __launch_bounds__(kFftThreads, 1)
@@ -177,7 +196,7 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
     constexpr int L = P::L, S = P::S1;
     static_assert(S == kFftThreads, "one pass-1 / last-pass butterfly per thread");
     extern __shared__ __align__(16) float4 smem4[];
-    uint8_t *raw0 = reinterpret_cast<uint8_t *>(smem4) + ((P::kSmemBytes + 127) / 128) * 128;   // 2 x B staging
+    uint8_t *raw0 = reinterpret_cast<uint8_t *>(smem4) + kPersistSmemData;   // 2 x B staging
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ ItemMeta s_meta[2];
     __shared__ float s_val[kFftThreads / 32];
@@ -185,7 +204,8 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     float2 w_l = __ldg(&TN[2 * threadIdx.x]), w_n = __ldg(&TN[threadIdx.x]);   // W_L^low, W_N^low
-    MidTw mt = mid_twiddles<LOG2L>(TN);
+    float2 w_a = mid_twiddle<LOG2L, P::RA, P::SA>(TN);                          // W_512^(lane): mid pass A
+    float2 t32 = make_float2(kW32c[lane & 15], kW32s[lane & 15]);               // conj(W_32^(lane & 15)): inverse 32-point stage
 
     // thread 0 owns the ticket: `tk` is the ticket of the item AFTER the one being staged, drawn one
     // phase ahead so that its latency is never waited for
@@ -220,7 +240,7 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
         // memory.  Recomputing them per item (as the one-item-per-CTA kernel does) is cheaper than that traffic.
 #ifndef COH_CORR_HOIST
         asm volatile("" : "+f"(w_l.x), "+f"(w_l.y), "+f"(w_n.x), "+f"(w_n.y));
-        asm volatile("" : "+f"(mt.a.x), "+f"(mt.a.y), "+f"(mt.b.x), "+f"(mt.b.y));
+        asm volatile("" : "+f"(w_a.x), "+f"(w_a.y), "+f"(t32.x), "+f"(t32.y));
 #endif
         if (threadIdx.x == 0 && cur.valid) {                // item i+1: its staging buffer was last read in X(i-1)
             stage(tk, buf ^ 1);
@@ -229,13 +249,13 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
         // ---- X(i) -------------------------------------------------------------------------------
         if (prev.valid) {
             float best = -1.0f; uint32_t bidx = 0xffffffffu;
-            last_pass_argmax<LOG2L>(smem4, w_l, w_n, best, bidx);
+            last_pass_argmax<LOG2L, 5>(smem4, w_l, w_n, best, bidx);
             warp_argmax(best, bidx);
             if (lane == 0) { s_val[warp] = best; s_idx[warp] = bidx; }
         }
         if (cur.valid) {
             mbar_wait(smem_u32(&s_bar[buf]), (i >> 1) & 1u);
-            pass1_butterfly<LOG2L, false>(raw0 + (size_t)buf * B, xormask, smem4, threadIdx.x, w_l, w_n);
+            pass1_butterfly<LOG2L, false, 5>(raw0 + (size_t)buf * B, xormask, smem4, threadIdx.x, w_l, w_n);
         }
         __syncthreads();
         if (prev.valid && warp == 0) {
@@ -246,10 +266,11 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
         }
         if (!cur.valid) break;
         // ---- M(i) -------------------------------------------------------------------------------
-        mid_passes<LOG2L, -1>(smem4, mt);
-        pair_correlate<LOG2L>(smem4, refspec + (size_t)cur.slot * L);
-        mid_sync<LOG2L>();
-        mid_passes<LOG2L, +1>(smem4, mt);
+        mid_pass<LOG2L, P::RA, P::SA, -1, 5>(smem4, w_a);          // radix 16 at stride 32
+        __syncwarp();
+        fused_b_stage<LOG2L>(smem4, refspec + (size_t)cur.slot * L);   // 32-point stage, x conj(R), inverse 16-point DFT
+        __syncwarp();
+        inv_a_stage<LOG2L>(smem4, w_a, t32);                       // radix 16 at stride 32, decimation in time
         __syncthreads();
         prev = cur;
     }
@@ -268,14 +289,32 @@ static cudaError_t launch_ref_t(const CorrLaunch &p, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         attr_done[dev & 63] = true;
     }
-    if (p.n_ref_blocks)
-        k_ref_spectrum<LOG2L><<<p.n_ref_blocks, kFftThreads, P::kSmemBytes, st>>>(
-            p.iq, (size_t)p.nch * p.B, p.ref_block_list, p.xormask, p.TN, reinterpret_cast<float4 *>(p.refspec));
+    bool fused = false;
+#ifndef COH_CORRELATE_V1
+    fused = LOG2L == 13 && p.ticket != nullptr;          // persistent kernel + its reference-spectrum layout
+#endif
+    if (p.n_ref_blocks) {
+        if constexpr (LOG2L == 13) {
+            if (fused) {
+                static bool attr3[64] = {};
+                if (!attr3[dev & 63]) {
+                    cudaError_t e = cudaFuncSetAttribute(k_ref_spectrum_fused<LOG2L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPersistSmemData);
+                    if (e != cudaSuccess) return e;
+                    attr3[dev & 63] = true;
+                }
+                k_ref_spectrum_fused<LOG2L><<<p.n_ref_blocks, kFftThreads, kPersistSmemData, st>>>(
+                    p.iq, (size_t)p.nch * p.B, p.ref_block_list, p.xormask, p.TN, reinterpret_cast<float4 *>(p.refspec));
+            }
+        }
+        if (!fused)
+            k_ref_spectrum<LOG2L><<<p.n_ref_blocks, kFftThreads, P::kSmemBytes, st>>>(
+                p.iq, (size_t)p.nch * p.B, p.ref_block_list, p.xormask, p.TN, reinterpret_cast<float4 *>(p.refspec));
+    }
     if (p.n_items) {
 #ifndef COH_CORRELATE_V1
         if constexpr (LOG2L == 13) {
             if (p.ticket) {
-                const size_t smem = ((P::kSmemBytes + 127) / 128) * 128 + 2 * (size_t)p.B;
+                const size_t smem = kPersistSmemData + 2 * (size_t)p.B;
                 static bool attr2[64] = {};
                 if (!attr2[dev & 63]) {
                     cudaError_t e = cudaFuncSetAttribute(k_correlate_persist<LOG2L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

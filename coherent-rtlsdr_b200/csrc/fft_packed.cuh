@@ -113,5 +113,9 @@ __device__ __forceinline__ void twiddle_pairs(PC t0, float2 w, PC (&T)[R]) {
 // stride-2^j column accesses of all passes on distinct 16-byte bank groups
 __host__ __device__ __forceinline__ int ppad(int a) { return a + (a >> 4); }
 __host__ __device__ constexpr int ppadded_len(int n) { return n + (n >> 4) + 1; }
+// the same with the padding distance as a parameter: PADSH = 4 is ppad(); PADSH = 5 (one pad element per 32)
+// is what the fused 32-point stage of the persistent L = 8192 kernel needs (fft_passes.cuh, fused_b_stage)
+template <int PADSH> __host__ __device__ __forceinline__ int ppad_t(int a) { return a + (a >> PADSH); }
+template <int PADSH> __host__ __device__ constexpr int ppadded_len_t(int n) { return n + (n >> PADSH) + 1; }
 
 }  // namespace coh

@@ -64,7 +64,7 @@ struct TwPair {
 };
 
 // ---- pass 1: global bytes -> shared, radix 16 at stride L/16, both halves ------------------
-template <int LOG2L, bool NEG_B>
+template <int LOG2L, bool NEG_B, int PADSH = 4>
 __device__ __forceinline__ void pass1_butterfly(const uint8_t *x, uint32_t xormask, float4 *s, int low,
                                                 float2 w_l, float2 w_n) {
     constexpr int S = Plan<LOG2L>::S1;
@@ -80,7 +80,7 @@ __device__ __forceinline__ void pass1_butterfly(const uint8_t *x, uint32_t xorma
     if (NEG_B) g = make_float2(-g.x, -g.y);           // ref sits in [L,2L): odd bins change sign
     const TwPair tw(w_l, g);                          // W_L^low
 #pragma unroll
-    for (int k = 0; k < 16; k++) s[ppad(low + k * S)] = pc_to(tw.apply(v[k], k));
+    for (int k = 0; k < 16; k++) s[ppad_t<PADSH>(low + k * S)] = pc_to(tw.apply(v[k], k));
 }
 template <int LOG2L, bool NEG_B>
 __device__ __forceinline__ void pass1_from_global(const uint8_t *x, uint32_t xormask, float4 *s,
@@ -119,7 +119,7 @@ __device__ __forceinline__ MidTw mid_twiddles(const float2 *__restrict__ TN) {
     return t;
 }
 
-template <int LOG2L, int R, int S, int DIR>
+template <int LOG2L, int R, int S, int DIR, int PADSH = 4>
 __device__ __forceinline__ void mid_pass(float4 *s, float2 w) {
     using P = Plan<LOG2L>;
     constexpr int NB = P::L / R;                      // butterflies
@@ -132,7 +132,7 @@ __device__ __forceinline__ void mid_pass(float4 *s, float2 w) {
         const TwScalar tw(w);
         PC v[R];
 #pragma unroll
-        for (int k = 0; k < R; k++) v[k] = pc_from(s[ppad(base + k * S)]);
+        for (int k = 0; k < R; k++) v[k] = pc_from(s[ppad_t<PADSH>(base + k * S)]);
         if (DIR > 0) {
 #pragma unroll
             for (int k = 1; k < R; k++) v[k] = tw.apply(v[k], k);
@@ -143,7 +143,7 @@ __device__ __forceinline__ void mid_pass(float4 *s, float2 w) {
             for (int k = 1; k < R; k++) v[k] = tw.apply(v[k], k);
         }
 #pragma unroll
-        for (int k = 0; k < R; k++) s[ppad(base + k * S)] = pc_to(v[k]);
+        for (int k = 0; k < R; k++) s[ppad_t<PADSH>(base + k * S)] = pc_to(v[k]);
     }
 }
 
@@ -224,6 +224,97 @@ __device__ __forceinline__ void pair_correlate(float4 *s, const float4 *__restri
             s[ppad(2 * m + 1 - sw)] = sw ? o0 : o1;
         }
     }
+}
+
+// ---- fused 32-point stage of the persistent L = 8192 kernel -------------------------------------------
+// After pass 1 (radix 16, stride 512) and mid pass A (radix 16, stride 32) the data is 256 contiguous
+// 32-point sub-transforms, 16 per warp.  Instead of radix 16 at stride 2 + a pair stage (two more
+// shared-memory round trips, the second with hardly any arithmetic between its loads and stores -- 20 % of
+// the kernel's time in profiles/r2_ncu_k_correlate_persist_v1.txt), TWO lanes share one 32-point group g:
+// both read all 32 elements (the lanes l and l + 16 of a warp read the same addresses), lane `half` = 0
+// forms the sums s[j] = e[j] + e[j+16], lane `half` = 1 the differences d[j] = (e[j] - e[j+16]) W_32^j, and
+// each finishes with a 16-point DFT in registers: the even / odd bins of the group.  The product with the
+// conjugate reference spectrum (cdsp::conjugatemul, src/cdsp.cc:105-108) and the first inverse 16-point DFT
+// follow in the same registers; what is stored back are the two half-results E and O, which the inverse mid
+// pass A combines on load (inv_a_stage): y[j] = E[j] + conj(W_32^j) O[j], y[j+16] = E[j] - conj(W_32^j) O[j].
+// Shared-memory padding for these passes: one element per 32 (ppad_t<5>), which keeps the stride-33 group
+// accesses of a quarter-warp on distinct 16-byte bank groups.
+//
+// Reference-spectrum layout for this path: bin n (0..15) of lane `lane` of warp w at
+// R[(w * 16 + n) * 32 + lane] -- k_ref_spectrum runs the same forward code and stores its registers, so the
+// order is consistent by construction and every load is one coalesced 512-byte row.
+template <int LOG2L>
+__device__ __forceinline__ void fused_b_load(const float4 *s, PC (&v)[16]) {
+    static_assert(LOG2L == 13 && kFftThreads == 512, "16 groups of 32 points per warp");
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int half = lane >> 4, base = warp * 512 + (lane & 15) * 32;
+    const float2 sg = splat(half ? -1.0f : 1.0f);
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const PC lo = pc_from(s[ppad_t<5>(base + j)]), hi = pc_from(s[ppad_t<5>(base + 16 + j)]);
+        PC d; d.r = __ffma2_rn(hi.r, sg, lo.r); d.i = __ffma2_rn(hi.i, sg, lo.i);   // e[j] +- e[j+16]
+        if (j == 0) { v[j] = d; continue; }
+        // W_32^j = exp(-2 pi i j / 32) on the difference lane, 1 on the sum lane
+        const float c = half ? kW32c[j] : 1.0f, sn = half ? -kW32s[j] : 0.0f;
+        v[j] = pc_mul(d, make_float2(c, sn));
+    }
+    PDft<16, -1>::run(v);
+}
+
+// k_ref_spectrum: the registers of fused_b_load are the spectrum
+template <int LOG2L>
+__device__ __forceinline__ void fused_b_out(const float4 *s, float4 *__restrict__ R) {
+    PC v[16];
+    fused_b_load<LOG2L>(s, v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int n = 0; n < 16; n++) R[(warp * 16 + n) * 32 + lane] = pc_to(v[n]);
+}
+
+// k_correlate: forward 32-point stage, x conj(R), first inverse 16-point DFT
+template <int LOG2L>
+__device__ __forceinline__ void fused_b_stage(float4 *s, const float4 *__restrict__ R) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float4 *Rw = R + (warp * 16) * 32 + lane;
+    float4 r0[8];                                       // first half of the spectrum rows in flight across the DFT
+#pragma unroll
+    for (int n = 0; n < 8; n++) r0[n] = __ldg(Rw + n * 32);
+    PC v[16];
+    fused_b_load<LOG2L>(s, v);
+    float4 r1[8];
+#pragma unroll
+    for (int n = 0; n < 8; n++) r1[n] = __ldg(Rw + (8 + n) * 32);
+#pragma unroll
+    for (int n = 0; n < 8; n++) v[n] = pc_mulcp(v[n], pc_from(r0[n]));
+#pragma unroll
+    for (int n = 0; n < 8; n++) v[8 + n] = pc_mulcp(v[8 + n], pc_from(r1[n]));
+    PDft<16, +1>::run(v);
+    const int base = warp * 512 + (lane & 15) * 32 + (lane >> 4) * 16;
+    __syncwarp();                                       // the partner lane has read what is overwritten now
+#pragma unroll
+    for (int j = 0; j < 16; j++) s[ppad_t<5>(base + j)] = pc_to(v[j]);
+}
+
+// inverse mid pass A (radix 16, stride 32, decimation in time) reading the E / O halves the fused stage left
+template <int LOG2L>
+__device__ __forceinline__ void inv_a_stage(float4 *s, float2 w, float2 t32) {
+    // w = W_512^low (forward twiddle base of mid pass A), t32 = conj(W_32^(low & 15))
+    const int warp = threadIdx.x >> 5, low = threadIdx.x & 31;
+    const int sub = warp * 512, jl = low & 15;
+    const float2 sg = splat((low >> 4) ? -1.0f : 1.0f);
+    const TwScalar tw(cconj(w));
+    PC v[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const PC E = pc_from(s[ppad_t<5>(sub + 32 * k + jl)]), O = pc_from(s[ppad_t<5>(sub + 32 * k + 16 + jl)]);
+        const PC t = pc_mul(O, t32);
+        PC y; y.r = __ffma2_rn(t.r, sg, E.r); y.i = __ffma2_rn(t.i, sg, E.i);
+        v[k] = k ? tw.apply(y, k) : y;
+    }
+    PDft<16, +1>::run(v);
+    __syncwarp();                                       // lanes low and low ^ 16 read each other's slots
+#pragma unroll
+    for (int k = 0; k < 16; k++) s[ppad_t<5>(sub + low + 32 * k)] = pc_to(v[k]);
 }
 
 }  // namespace coh

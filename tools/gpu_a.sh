@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 timeout 120 python __graft_entry__.py smoke > gpurun_out/r2a_smoke.txt 2>&1; tail -3 gpurun_out/r2a_smoke.txt
 timeout 900 python -m pytest tests -m gpu -q > gpurun_out/r2a_pytest.txt 2>&1; tail -30 gpurun_out/r2a_pytest.txt
-for v in "" _v1 _hoist; do
+for v in ""; do
   COHCUDA_LIB=$PWD/coherent-rtlsdr_b200/lib/libcoherent_cuda$v.so timeout 200 python bench.py --steps 10 --warmup 3 --no-cpu > gpurun_out/r2a_bench1$v.json 2> gpurun_out/r2a_bench1$v.err
   tail -c 300 gpurun_out/r2a_bench1$v.err
   python - <<PY
