@@ -40,6 +40,7 @@ CONFIG = "ura21"
 PRESETS = {"ura21": (21, 16384, 1024), "four": (3, 16384, 64), "big65536": (21, 131072, 256),
            "stream": (21, 16384, 1024)}
 REQ = None                        # host [n_blocks][C+1] lag-request flags for --mode mixed
+STEPS = None                      # [(block, channel, new delay)] delay steps of --mode mixed
 BYTES_PER_SAMPLE = 4.0            # 2 B u8 IQ in + 2 B int8 IQ out (packet mode)
 FLOP_PER_SAMPLE_SYNC = 311.0      # SURVEY 8d algorithmic flops per coherent sample, SYNC mode
 
@@ -113,10 +114,12 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None}
 
 
-def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64, ref_seed=None):
+def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=64, ref_seed=None, delay_steps=None):
     """Synthetic IQ of SURVEY 8d generated on the device (same model as synth.make_blocks).
     ref_seed: seed of the reference-noise stream when it is shared by several channel groups
-    (config 4: every rank's 21 channels see the same reference); default = seed."""
+    (config 4: every rank's 21 channels see the same reference); default = seed.
+    delay_steps: [(block, channel 1.., new_delay)] -- the channel's delay changes from that block on (drift /
+    re-sync scenario of config 5); returns the per-block delay matrix as 4th value when given."""
     L = blocksize // 2
     gr = torch.Generator(device=device); gr.manual_seed(seed if ref_seed is None else ref_seed)
     g = torch.Generator(device=device); g.manual_seed(seed ^ 0x5EED)
@@ -132,13 +135,24 @@ def gen_device_iq(torch, n_signal, blocksize, n_blocks, seed, device, max_delay=
         return torch.clamp(torch.round(v + 127.5), 0, 255).to(torch.uint8)
 
     iq[:, 0, :] = quant(r[pad:pad + n_blocks * L]).reshape(n_blocks, blocksize)
+    dmat = np.tile(np.asarray(delays, dtype=np.int64), (n_blocks, 1))
+    for (b0, ch, nd) in (delay_steps or []):
+        assert abs(nd) <= max_delay
+        dmat[b0:, ch - 1] = nd
+    ar = torch.arange(L, device=device)
     for k in range(n_signal):
-        s = pad - int(delays[k])
-        seg = r[s:s + n_blocks * L]
+        if delay_steps:
+            start = torch.as_tensor(pad + np.arange(n_blocks) * L - dmat[:, k], device=device)
+            seg = r[(start[:, None] + ar[None, :]).reshape(-1)]
+        else:
+            s = pad - int(delays[k])
+            seg = r[s:s + n_blocks * L]
         c, sn = float(gains[k] * np.cos(phases[k])), float(gains[k] * np.sin(phases[k]))
         w = torch.randn(n_blocks * L, 2, generator=g, device=device) * 4.0
         x = torch.stack((seg[:, 0] * c - seg[:, 1] * sn, seg[:, 0] * sn + seg[:, 1] * c), dim=1) + w
         iq[:, k + 1, :] = quant(x).reshape(n_blocks, blocksize)
+    if delay_steps:
+        return iq, delays, phases, dmat
     return iq, delays, phases
 
 
@@ -406,7 +420,14 @@ def run_gpu_arm(args):
     eng = pkg.CoherentCuda(C_SIG, B, apply_shift=True, device=local, max_batch_blocks=nb,
                            stream=stream.cuda_stream, alpha=args.alpha)
     # each rank holds its own 21 signal channels and its own copy of the ONE shared reference channel
-    iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev, ref_seed=0xC0DE + 1)
+    dmat = None
+    if args.mode == "mixed":
+        # config 5's drift re-sync: delays STEP at known blocks, the channel asks for its lag again there
+        # (src/console.cc:285-289 -> include/csdrdevice.h:129-151), every fifth request three blocks late
+        iq, delays, _, dmat = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev, ref_seed=0xC0DE + 1,
+                                            delay_steps=STEPS)
+    else:
+        iq, delays, _ = gen_device_iq(torch, C_SIG, B, nb, 0xC0DE + 1 + 1000 * rank, dev, ref_seed=0xC0DE + 1)
     pk_dev = torch.zeros(nb * eng.dev_pitch + 16, dtype=torch.int8, device=dev)
     torch.cuda.synchronize()
     samples_per_step = nch * L * nb
@@ -508,6 +529,10 @@ def run_gpu_arm(args):
     ms_e2e = timed(step_e2e, max(args.steps // 2, 2), 3)
     e2e_steps = max(args.steps // 2, 2)
     lag_ok = bool((h_lag[:, 1:].numpy() == delays[None, :]).all()) if args.mode == "sync" else None
+    if args.mode == "mixed":
+        # every served request must return the delay in force AT THAT BLOCK, and the lag held afterwards is that one
+        served = REQ[:, 1:].astype(bool)
+        lag_ok = bool((h_lag[:, 1:].numpy()[served] == dmat[served]).all())
 
     # ---- sustained run (BASELINE configs[4] is "sustained throughput"): seconds, not a 50 ms burst ----------
     sustained = None
@@ -619,15 +644,23 @@ def main():
     ap.add_argument("--store-ctas", type=int, default=0, help="CTAs of the NVLink-storing k_apply (0 = library default)")
     ap.add_argument("--gather-verify-all", action="store_true", help="compare every gathered block, not a sample")
     args = ap.parse_args()
-    global C_SIG, BLOCKSIZE, N_BLOCKS, CONFIG, REQ
+    global C_SIG, BLOCKSIZE, N_BLOCKS, CONFIG, REQ, STEPS
     CONFIG = args.config
     C_SIG, BLOCKSIZE, N_BLOCKS = PRESETS[CONFIG]
     if args.blocks == 1024:
         args.blocks = N_BLOCKS
     if args.mode == "mixed":
         rng = np.random.default_rng(5)
-        REQ = (rng.random((args.blocks, C_SIG + 1)) < 0.01).astype(np.uint8)
-        REQ[0, 1:] = 1; REQ[:, 0] = 0
+        # about 1 % of the (block, channel) items re-request a lag; every one of them follows a delay step
+        n_steps = max(1, int(0.01 * args.blocks * C_SIG))
+        REQ = np.zeros((args.blocks, C_SIG + 1), np.uint8); REQ[0, 1:] = 1
+        STEPS = []
+        for i in range(n_steps):
+            b0 = int(rng.integers(1, max(args.blocks - 4, 2))); ch = int(rng.integers(1, C_SIG + 1))
+            STEPS.append((b0, ch, int(rng.integers(-64, 65))))
+        STEPS.sort()
+        for i, (b0, ch, _) in enumerate(STEPS):
+            REQ[min(b0 + (3 if i % 5 == 0 else 0), args.blocks - 1), ch] = 1
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -143,21 +143,23 @@ __device__ __forceinline__ void dot_segment(uint4 *sx, const uint4 *__restrict__
     for (int t0 = 0; t0 < seg_chunks; t0 += 32 * kU) {     // warp-uniform trip count (syncwarp inside)
         const int jj0 = t0 + lane;
         uint4 xv[kU], rn[kU];
+        {
 #pragma unroll
-        for (int u = 0; u < kU; u++) {                    // reference samples of the NEXT trip
-            const int jn = jj0 + 32 * (u + kU);
-            rn[u] = jn < seg_chunks ? __ldg(rin + jn) : z;
-        }
+            for (int u = 0; u < kU; u++) {                    // reference samples of the NEXT trip
+                const int jn = jj0 + 32 * (u + kU);
+                rn[u] = jn < seg_chunks ? __ldg(rin + jn) : z;
+            }
 #pragma unroll
-        for (int u = 0; u < kU; u++) {
-            const int jj = jj0 + 32 * u;
-            xv[u] = read_shifted<K, TOSIGNED>(sx, jj < seg_chunks ? jj : 0, jj < seg_chunks ? a_base + jj : -2, nchunks);
-        }
-        __syncwarp();
+            for (int u = 0; u < kU; u++) {
+                const int jj = jj0 + 32 * u;
+                xv[u] = read_shifted<K, TOSIGNED>(sx, jj < seg_chunks ? jj : 0, jj < seg_chunks ? a_base + jj : -2, nchunks);
+            }
+            __syncwarp();
 #pragma unroll
-        for (int u = 0; u < kU; u++) {
-            const int jj = jj0 + 32 * u;
-            if (jj < seg_chunks) sx[jj] = xv[u];
+            for (int u = 0; u < kU; u++) {
+                const int jj = jj0 + 32 * u;
+                if (jj < seg_chunks) sx[jj] = xv[u];
+            }
         }
 #pragma unroll
         for (int u = 0; u < kU; u++) {
