@@ -39,6 +39,7 @@ CONFIG = "ura21"
 # configs[3] (168 channels, channel groups of 21 per GPU) is the ura21 line at --gpus 8 with_gather.
 PRESETS = {"ura21": (21, 16384, 1024), "four": (3, 16384, 64), "big65536": (21, 131072, 256),
            "stream": (21, 16384, 1024)}
+CONFIG_INDEX = {"four": 0, "ura21": 1, "big65536": 2, "stream": 4}   # index into BASELINE.json "configs" (3 = ura21 at --gpus 8 with_gather)
 REQ = None                        # host [n_blocks][C+1] lag-request flags for --mode mixed
 STEPS = None                      # [(block, channel, new delay)] delay steps of --mode mixed
 BYTES_PER_SAMPLE = 4.0            # 2 B u8 IQ in + 2 B int8 IQ out (packet mode)
@@ -561,10 +562,9 @@ def run_gpu_arm(args):
             "ms_per_step": ms_main / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{CONFIG}: {C_SIG}+1 channels x {L}-sample blocks x {nb} blocks per GPU "
-                                   f"(BASELINE.json configs[{list(PRESETS).index(CONFIG) if CONFIG != 'stream' else 4}]"
-                                   f"{' = URA21' if CONFIG == 'ura21' else ''}), {args.mode.upper()} mode, software shift on",
+                                   f"(BASELINE.json configs[{CONFIG_INDEX[CONFIG]}]), {args.mode.upper()} mode, software shift on",
                        "mode": args.mode, "blocks_per_gpu": nb, "channels": nch, "L": L,
-                       "parallelism": f"block-sharded x{world}, ref channel replicated",
+                       "parallelism": f"{world} x {C_SIG} signal channels, one shared reference channel replicated to every rank" if world > 1 else "single GPU",
                        "l2": f"input {nb * nch * B >> 20} MiB + output {nb * nch * B >> 20} MiB per step exceed the 126 MB L2 (no flush needed)"},
             "roofline": roofline(args.mode),
             "modes": {args.mode: {"value": val(ms_main, args.steps), "ms_per_step": ms_main / args.steps},
