@@ -266,9 +266,11 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
         }
         if (!cur.valid) break;
         // ---- M(i) -------------------------------------------------------------------------------
+        float4 r_early[kEarly ? kEarly : 1];
+        fused_b_early<LOG2L>(refspec + (size_t)cur.slot * L, r_early);
         mid_pass<LOG2L, P::RA, P::SA, -1, 5>(smem4, w_a);          // radix 16 at stride 32
         __syncwarp();
-        fused_b_stage<LOG2L>(smem4, refspec + (size_t)cur.slot * L);   // 32-point stage, x conj(R), inverse 16-point DFT
+        fused_b_stage<LOG2L>(smem4, refspec + (size_t)cur.slot * L, r_early);   // 32-point stage, x conj(R), inverse 16-point DFT
         __syncwarp();
         inv_a_stage<LOG2L>(smem4, w_a, t32);                       // radix 16 at stride 32, decimation in time
         __syncthreads();

@@ -271,14 +271,28 @@ __device__ __forceinline__ void fused_b_out(const float4 *s, float4 *__restrict_
     for (int n = 0; n < 16; n++) R[(warp * 16 + n) * 32 + lane] = pc_to(v[n]);
 }
 
-// k_correlate: forward 32-point stage, x conj(R), first inverse 16-point DFT
+// k_correlate: forward 32-point stage, x conj(R), first inverse 16-point DFT.  The spectrum rows come from L2
+// (one 128 KiB spectrum per block, shared by the block's channels): kEarly of this lane's sixteen rows are
+// requested by the caller ahead of mid pass A (r_early), the next 8 - kEarly before the 32-point stage's own
+// shared-memory loads, the last eight behind the DFT.
+#ifndef COH_R_EARLY
+#define COH_R_EARLY 8       // measured 0 / 4 / 8: 1.735 / 1.772 / 1.717 ms per 21 504 items (profiles/r2_correlate_history.md)
+#endif
+constexpr int kEarly = COH_R_EARLY;
 template <int LOG2L>
-__device__ __forceinline__ void fused_b_stage(float4 *s, const float4 *__restrict__ R) {
+__device__ __forceinline__ void fused_b_early(const float4 *__restrict__ R, float4 (&re)[kEarly ? kEarly : 1]) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float4 *Rw = R + (warp * 16) * 32 + lane;
+#pragma unroll
+    for (int n = 0; n < kEarly; n++) re[n] = __ldg(Rw + n * 32);
+}
+template <int LOG2L>
+__device__ __forceinline__ void fused_b_stage(float4 *s, const float4 *__restrict__ R, const float4 (&re)[kEarly ? kEarly : 1]) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float4 *Rw = R + (warp * 16) * 32 + lane;
     float4 r0[8];                                       // first half of the spectrum rows in flight across the DFT
 #pragma unroll
-    for (int n = 0; n < 8; n++) r0[n] = __ldg(Rw + n * 32);
+    for (int n = 0; n < 8; n++) r0[n] = n < kEarly ? re[n] : __ldg(Rw + n * 32);
     PC v[16];
     fused_b_load<LOG2L>(s, v);
     float4 r1[8];
