@@ -38,9 +38,15 @@
 
 namespace coh {
 
-constexpr int kWarpsPerCta = 13;                          // 13 independent warps, one CTA per SM
+#ifndef COH_APPLY_WARPS
+#define COH_APPLY_WARPS 13
+#endif
+#ifndef COH_APPLY_SEG
+#define COH_APPLY_SEG 16384
+#endif
+constexpr int kWarpsPerCta = COH_APPLY_WARPS;             // independent warps, one CTA per SM
 constexpr int kApplyThreads = 32 * kWarpsPerCta;
-constexpr uint32_t kSegBytes = 16384;                     // shared-memory resident part of a row
+constexpr uint32_t kSegBytes = COH_APPLY_SEG;             // shared-memory resident part of a row
 constexpr uint32_t kScratchBytes = 512;                   // look-back scratch: 64 x float2
 // + one chunk of overlap for the shift; padded to a multiple of 128 B so that every warp's buffer starts on a
 // bank-row boundary (a pitch of 16928 = 32 mod 128 made 12 of 13 warps' LDS.128 bursts straddle five bank rows:

@@ -57,40 +57,56 @@ k_big_split(const BigAddr a, uint32_t xormask, const float2 *__restrict__ TN, fl
     for (int k = 0; k < Q; k++) o[(size_t)k * kSub] = pc_to(tw.apply(v[k], k));
 }
 
-// grid items * Q; data[item][Q][8192] transformed in place
+// grid items * Q; data[item][Q][8192] transformed in place.  Same middle phase as the persistent L = 8192
+// kernel (fft_kernels.cu): radix 16 at stride 32, fused 32-point stage with X * conj(R) and the first inverse
+// 16-point DFT, inverse radix 16 at stride 32 -- five shared-memory round trips instead of seven; the reference
+// spectrum of a sub-sequence is kept in the register order of that stage (fused_b_out).
+constexpr size_t kBigSubSmem = ((size_t)ppadded_len_t<5>(kSub) * sizeof(float4) + 127) / 128 * 128;
 template <bool REFONLY>
 __global__ void __launch_bounds__(kFftThreads, 1)
 k_big_sub(float4 *__restrict__ data, int Q, const BigAddr a, const float4 *__restrict__ refspec,
           const float2 *__restrict__ TNs) {
     using P = Plan<kSubLog2>;
     constexpr int S = P::S1;
+    static_assert(S == kFftThreads, "one butterfly per thread in the first and last pass");
     extern __shared__ __align__(16) float4 smem4[];
     const uint32_t it = blockIdx.x / Q, q0 = blockIdx.x % Q;
     float4 *d = data + ((size_t)it * Q + q0) * kSub;
-    for (int low = threadIdx.x; low < S; low += kFftThreads) {
+    const int low = threadIdx.x;
+    const float2 w_s = __ldg(&TNs[2 * low]);                                    // W_8192^low
+    const float2 w_a = mid_twiddle<kSubLog2, P::RA, P::SA>(TNs);                // W_512^(lane)
+    const float4 *R = nullptr;
+    if (!REFONLY) {
+        uint32_t b, c;
+        item_bc(a, it, b, c);
+        const uint32_t slot = a.block_slot ? a.block_slot[b] : b;
+        R = refspec + ((size_t)slot * Q + q0) * kSub;
+    }
+    {
         PC v[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) v[k] = pc_from(d[low + k * S]);
         PDft<16, -1>::run(v);
-        const TwScalar tw(__ldg(&TNs[2 * low]));
+        const TwScalar tw(w_s);
 #pragma unroll
-        for (int k = 0; k < 16; k++) smem4[ppad(low + k * S)] = pc_to(tw.apply(v[k], k));
+        for (int k = 0; k < 16; k++) smem4[ppad_t<5>(low + k * S)] = pc_to(tw.apply(v[k], k));
     }
     __syncthreads();
-    mid_passes<kSubLog2, -1>(smem4, TNs);
-    if (REFONLY) { pair_out<kSubLog2>(smem4, d); return; }
-    uint32_t b, c;
-    item_bc(a, it, b, c);
-    const uint32_t slot = a.block_slot ? a.block_slot[b] : b;
-    pair_correlate<kSubLog2>(smem4, refspec + ((size_t)slot * Q + q0) * kSub);
-    mid_sync<kSubLog2>();
-    mid_passes<kSubLog2, +1>(smem4, TNs);
-    if constexpr (WarpLocal<kSubLog2>::value) __syncthreads();
-    for (int low = threadIdx.x; low < S; low += kFftThreads) {
+    float4 r_early[kEarly ? kEarly : 1];
+    if (!REFONLY) fused_b_early<kSubLog2>(R, r_early);
+    mid_pass<kSubLog2, P::RA, P::SA, -1, 5>(smem4, w_a);
+    __syncwarp();
+    if (REFONLY) { fused_b_out<kSubLog2>(smem4, d); return; }
+    fused_b_stage<kSubLog2>(smem4, R, r_early);
+    __syncwarp();
+    const int lane = threadIdx.x & 31;
+    inv_a_stage<kSubLog2>(smem4, w_a, make_float2(kW32c[lane & 15], kW32s[lane & 15]));
+    __syncthreads();
+    {
         PC v[16];
-        const TwScalar tw(cconj(__ldg(&TNs[2 * low])));
+        const TwScalar tw(cconj(w_s));
 #pragma unroll
-        for (int k = 0; k < 16; k++) v[k] = tw.apply(pc_from(smem4[ppad(low + k * S)]), k);
+        for (int k = 0; k < 16; k++) v[k] = tw.apply(pc_from(smem4[ppad_t<5>(low + k * S)]), k);
         PDft<16, +1>::run(v);
 #pragma unroll
         for (int k = 0; k < 16; k++) d[low + k * S] = pc_to(v[k]);
@@ -159,9 +175,9 @@ static cudaError_t launch_big_t(const CorrLaunch &p, cudaStream_t st) {
     static bool attr_done[64] = {};
     int dev = 0; cudaGetDevice(&dev);
     if (!attr_done[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(k_big_sub<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P::kSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute(k_big_sub<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBigSubSmem);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_big_sub<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P::kSmemBytes);
+        e = cudaFuncSetAttribute(k_big_sub<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBigSubSmem);
         if (e != cudaSuccess) return e;
         attr_done[dev & 63] = true;
     }
@@ -171,12 +187,12 @@ static cudaError_t launch_big_t(const CorrLaunch &p, cudaStream_t st) {
     float4 *spec = reinterpret_cast<float4 *>(p.refspec);
     if (p.n_ref_blocks) {
         k_big_split<Q, true><<<dim3(kSub / kSplitThreads, p.n_ref_blocks), kSplitThreads, 0, st>>>(a, p.xormask, p.TN, spec);
-        k_big_sub<true><<<p.n_ref_blocks * Q, kFftThreads, P::kSmemBytes, st>>>(spec, Q, a, nullptr, p.TN_sub);
+        k_big_sub<true><<<p.n_ref_blocks * Q, kFftThreads, kBigSubSmem, st>>>(spec, Q, a, nullptr, p.TN_sub);
     }
     if (p.n_items) {
         if (!p.scratch || !p.TN_sub) return cudaErrorInvalidValue;
         k_big_split<Q, false><<<dim3(kSub / kSplitThreads, p.n_items), kSplitThreads, 0, st>>>(a, p.xormask, p.TN, p.scratch);
-        k_big_sub<false><<<p.n_items * Q, kFftThreads, P::kSmemBytes, st>>>(p.scratch, Q, a, spec, p.TN_sub);
+        k_big_sub<false><<<p.n_items * Q, kFftThreads, kBigSubSmem, st>>>(p.scratch, Q, a, spec, p.TN_sub);
         k_big_merge<Q><<<p.n_items, kFftThreads, 0, st>>>(p.scratch, a, p.TN, p.peaks);
     }
     return cudaGetLastError();
