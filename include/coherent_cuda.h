@@ -43,7 +43,10 @@ typedef struct {
     uint32_t blocksize;         /* B bytes per channel-block = 2L, power of two, 64..131072 for
                                    the correlation path (src/main.cc:167 default 1<<14)       */
     uint32_t max_lag_slots;     /* reference: nfft-1 = 7 (src/ccoherent.cc:124); 0 = no cap   */
-    float    alpha;             /* phase IIR weight; reference 0.5 (src/csdrdevice.cc:60)     */
+    float    alpha;             /* phase IIR weight; reference 0.5 (src/csdrdevice.cc:60).  Range
+                                   [0.0162, 1]: the recurrence is evaluated as a look-back of
+                                   ceil(48 ln2 / -ln(1-alpha)) <= 2048 blocks (tail weight 2^-48),
+                                   which IS the sequential fp32 result; smaller alpha is rejected */
     int      noheader;          /* -R raw packets (src/cpacketizer.cc:91-96)                  */
     int      apply_shift;       /* 1: software integer-delay removal; 0: as ref   */
     int      device;            /* CUDA device ordinal                                        */
