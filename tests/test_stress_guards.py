@@ -70,3 +70,41 @@ def test_repeated_runs_are_bit_identical_under_contention(pkg, synth, oracle, mo
             np.testing.assert_array_equal(out["mag"].view(np.uint32), first["mag"].view(np.uint32))
             np.testing.assert_array_equal(out["phase"].view(np.uint32), first["phase"].view(np.uint32))
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("transport", ["nccl", "peer_copy", "peer_store"])
+@pytest.mark.parametrize("shard", ["channels", "blocks"])
+def test_gather_api_on_a_single_rank(pkg, synth, oracle, transport, shard):
+    """The library's gather path with a world of one (runs on a single-GPU box too): init / export / attach,
+    batches with gather = 1 (the second one with a block shard's warm-up halo), gather_fetch -- the gathered
+    packets are the rank's own packets, byte for byte, and the two gathered buffers alternate."""
+    C, B, nb = 4, 2048, 37
+    iq, _ = synth.make_blocks(C, B, nb, seed=404, delays=np.array([3, -9, 0, 21]))
+    eng = pkg.CoherentCuda(C, B, apply_shift=True)
+    want = eng.batch(iq, lag_mode=pkg.LAG_ALL, readcnt0=8, globalseqn0=5)
+    eng.close()
+    eng = pkg.CoherentCuda(C, B, apply_shift=True)
+    counts = [C] if shard == "channels" else [nb]
+    geo = eng.gather_init(0, 1, counts, pkg.SHARD_CHANNELS if shard == "channels" else pkg.SHARD_BLOCKS,
+                          pkg.TRANSPORTS[transport], max_blocks=nb, chunk_blocks=8)
+    assert (geo.packet_len, geo.dev_pitch, geo.dev_lead) == (eng.packet_len, eng.dev_pitch, eng.dev_lead)
+    assert geo.total_channels == C + 1 and geo.first_column == 1 and geo.first_block == 0
+    eng.gather_attach(eng.gather_export())
+    out = eng.batch(iq, lag_mode=pkg.LAG_ALL, readcnt0=8, globalseqn0=5, gather=True)
+    assert out["packets"] is None
+    np.testing.assert_array_equal(eng.gather_fetch(0, nb), want["packets"])
+    np.testing.assert_array_equal(out["lag"], want["lag"])
+    p0 = eng.gather_packets_ptr()
+    eng.batch(iq, lag_mode=pkg.LAG_NONE, gather=True)
+    assert eng.gather_packets_ptr() != p0                      # the other gathered buffer
+    if shard == "blocks":
+        # a shard with a warm-up halo: 12 leading blocks are computed but not gathered
+        eng2 = pkg.CoherentCuda(C, B, apply_shift=True)
+        eng2.gather_init(0, 1, [nb - 12], pkg.SHARD_BLOCKS, pkg.TRANSPORTS[transport], max_blocks=nb, chunk_blocks=8)
+        eng2.gather_attach(eng2.gather_export())
+        eng2.batch(iq, lag_mode=pkg.LAG_ALL, readcnt0=8, globalseqn0=5, gather=True, gather_skip_blocks=12)
+        np.testing.assert_array_equal(eng2.gather_fetch(0, nb - 12), want["packets"][12:])
+        eng2.close()
+    with pytest.raises(pkg.CohCudaError):
+        eng.batch(iq[:5], lag_mode=pkg.LAG_ALL, gather=True, gather_skip_blocks=9)       # halo longer than the call
+    eng.close()
