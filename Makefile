@@ -5,7 +5,7 @@ CSRC    := $(PKG)/csrc
 LIB     := $(PKG)/lib/libcoherent_cuda.so
 ARCH    := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := $(ARCH) -std=c++17 -O3 -lineinfo -Xcompiler -fPIC -Iinclude -I$(CSRC) --fmad=true
-OBJS    := $(CSRC)/api.o $(CSRC)/fft_kernels.o $(CSRC)/fft_big.o $(CSRC)/apply_kernel.o $(CSRC)/cov_kernel.o $(CSRC)/frac_kernel.o $(CSRC)/prims.o
+OBJS    := $(CSRC)/api.o $(CSRC)/fft_kernels.o $(CSRC)/fft_big.o $(CSRC)/apply_kernel.o $(CSRC)/cov_kernel.o $(CSRC)/frac_kernel.o $(CSRC)/prims.o $(CSRC)/lag_static.o
 
 all: $(LIB) oracle
 

@@ -37,8 +37,10 @@ ABI_SYMBOLS = [
     "cohcuda_cdsp_fft", "cohcuda_profile", "cohcuda_profile_read",
     "cohcuda_gather_plan", "cohcuda_gather_init", "cohcuda_gather_export", "cohcuda_gather_attach",
     "cohcuda_gather_geometry_of", "cohcuda_gather_packets", "cohcuda_gather_fetch", "cohcuda_gather_bytes",
-    "cohcuda_gather_destroy",
+    "cohcuda_gather_destroy", "cohcuda_lags_static",
 ]
+# limits of cohcuda_lags_static (include/coherent_cuda.h)
+STATIC_MAX_BLOCKSIZE, STATIC_MAX_SPECTRUM_BYTES, STATIC_MAX_ITEMS = 16384, 4 << 20, 4096
 
 
 class Config(C.Structure):
@@ -141,6 +143,8 @@ def load_library():
     L.cohcuda_cdsp_fft.argtypes = [vp, vp, vp, i, i, i]
     L.cohcuda_profile.argtypes = [vp, i]
     L.cohcuda_profile_read.argtypes = [vp, vp, vp]
+    if hasattr(L, "cohcuda_lags_static"):
+        L.cohcuda_lags_static.argtypes = [vp, u32, u32, u32, i, vp, vp, vp, C.c_char_p, C.c_size_t]
     if not hasattr(L, "cohcuda_gather_plan"):        # an older build of the library (kernel A/B experiments via COHCUDA_LIB)
         _lib = L
         return L
@@ -163,6 +167,21 @@ def _ptr(a):
     if isinstance(a, int):
         return a
     return a.ctypes.data
+
+
+def lags_static(iq_dev, n_signal, blocksize, n_blocks, lag_dev, mag_dev, input_is_signed=False, stream=None):
+    """cohcuda_lags_static: lag / mag of every (block, channel) without a handle and without any
+    allocation inside the library (its working memory is a fixed array in the library image; see
+    include/coherent_cuda.h for who needs that, the size limits and the sharing rules).  All three
+    buffers are DEVICE pointers (ints) on the current device: iq [n_blocks][n_signal+1][blocksize]
+    uint8, lag / mag [n_blocks][n_signal+1] float32.  Enqueues on ``stream`` (int cudaStream_t or
+    None) and returns; synchronise that stream before reading the outputs."""
+    lib = load_library()
+    err = C.create_string_buffer(512)
+    rc = lib.cohcuda_lags_static(iq_dev, n_signal, blocksize, n_blocks, int(bool(input_is_signed)),
+                                 lag_dev, mag_dev, stream, err, len(err))
+    if rc != 0:
+        raise CohCudaError(f"cohcuda_lags_static failed ({rc}): {err.value.decode()}")
 
 
 class CoherentCuda:

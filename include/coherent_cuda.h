@@ -181,6 +181,53 @@ int cohcuda_covariance(cohcuda_t *h, const int8_t *packets_dev, uint32_t n_block
 int cohcuda_fraclag(cohcuda_t *h, const uint8_t *iq_dev, uint32_t n_blocks, int input_is_signed,
                     float *frac_host, double *y3_host);
 
+/* ---- lag measurement without any allocation ------------------------------------------------------
+ * (No counterpart in the reference: it exists for the deployment constraint described here.)
+ *
+ * Who needs it.  Everything above works on a handle, and cohcuda_create() / cohcuda_batch() get their
+ * working memory from cudaMalloc.  Some programs that want the lag of a few blocks cannot do that: a
+ * receiver's DSP thread with a block period to keep (cudaMalloc and cudaFree serialise against the whole
+ * device and can stall it for longer than one 3.4 ms block); a plug-in living inside a host program
+ * whose own memory pool already owns the GPU, where a late cudaMalloc fails at some arbitrary block; a
+ * process whose policy is a fixed memory map with the CUDA allocator switched off.  This entry point
+ * needs no handle and reaches no cudaMalloc, cudaFree or allocating library call: its working memory
+ * (twiddle tables, reference spectra, peak records, the persistent kernel's ticket) is one fixed
+ * `static __device__` array inside the library, about 4.2 MiB, which every GPU that loads
+ * libcoherent_cuda.so holds from the process's first CUDA call until exit -- used or not.
+ *
+ * What it computes.  For iq_dev = [n_blocks][n_signal + 1][blocksize] raw bytes ON THE CURRENT DEVICE
+ * (channel 0 = reference, 16-byte aligned) it writes lag_dev / mag_dev = [n_blocks][n_signal + 1]
+ * floats, also device memory supplied by the caller: exactly the `lag` and `mag` cohcuda_batch()
+ * reports with lag_mode = COHCUDA_LAG_ALL (same kernels, bit-identical; entry 0 of each block is 0).
+ * The work is enqueued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns;
+ * the outputs are complete once that stream has been synchronised.
+ *
+ * Limits (the fixed array is the reason; beyond them the call fails with COHCUDA_ERR_UNSUPPORTED and
+ * a message naming the limit -- use cohcuda_batch for larger jobs, or split the call):
+ *   blocksize                  power of two, 64 .. COHCUDA_STATIC_MAX_BLOCKSIZE
+ *   n_blocks * 8 * blocksize   <= COHCUDA_STATIC_MAX_SPECTRUM_BYTES   (32 blocks of 16384 bytes)
+ *   n_blocks * (n_signal + 1)  <= COHCUDA_STATIC_MAX_ITEMS
+ *
+ * First call on each device.  It resolves the array's device address (cudaGetSymbolAddress), uploads
+ * the twiddle tables with a synchronous copy and waits for the device.  Make that first call -- any
+ * valid call will do -- during start-up, with the intended device current, and before any stream
+ * capture is begun; later calls on that device only launch kernels and one 4-byte cudaMemsetAsync.
+ *
+ * Sharing.  A process has ONE such array per device and every call uses it, whatever its stream or
+ * thread.  It keeps whatever the previous call left; the only word that must start at zero (the
+ * ticket) is cleared by each call itself, on its stream, and every other word is written before it is
+ * read.  Two calls whose GPU work overlaps in time (issued on different streams, from one thread or
+ * several) race on the array and return garbage: put them on one stream, or order them with events.
+ * Handles created by cohcuda_create() have their own buffers and are not affected.
+ *
+ * errbuf (optional, errbuf_len bytes) receives the message of a failed call; returns a cohcuda_status. */
+#define COHCUDA_STATIC_MAX_BLOCKSIZE      16384u
+#define COHCUDA_STATIC_MAX_SPECTRUM_BYTES (4u << 20)
+#define COHCUDA_STATIC_MAX_ITEMS          4096u
+int cohcuda_lags_static(const uint8_t *iq_dev, uint32_t n_signal, uint32_t blocksize, uint32_t n_blocks,
+                        int input_is_signed, float *lag_dev, float *mag_dev, void *stream,
+                        char *errbuf, size_t errbuf_len);
+
 /* ---- multi-GPU: the gather of the corrected matrix to one rank -------------------
  * One process and one handle per GPU.  The path shards with no exchange inside the arithmetic;
  * the only collective is the gather of the packed int8 packets to the rank that feeds the
