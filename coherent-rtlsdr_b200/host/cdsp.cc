@@ -23,6 +23,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <utility>
+#include <vector>
 
 #include "coherent_cuda.h"
 #include "cohcuda_host.h"
@@ -83,28 +85,78 @@ extern "C" void cohcuda_host_destroy_fft_scheme(void *scheme) { delete (cohcuda_
 // its load; column 0 of the packet is then taken from the library's packet, not from the
 // raw buffer.  Out-of-place calls (a caller that wants the converted bytes) still run the kernel.
 // COHCUDA_HOST_XOR_ON_CALL=1 restores the convert-at-call behaviour for in-place calls too.
+//
+// The primitive's contract is kept for everyone who reads such a buffer THROUGH cdsp:: -- a deferred
+// range is remembered, and cdsp::convtofloat (the only cdsp:: static that reads int8) applies the
+// pending ^0x80 on the device when its source lies inside one.  That is the path of the reference's
+// console `phase` command (src/console.cc:295-299: d->convtofloat() then est_phasecorrect() on the ring
+// buffers).  Code that reads the raw bytes of a deferred buffer directly still sees offset-binary
+// (cohcuda_host_xor_pending() tells); the replaced ccoherent thread is the one such reader.
 extern "C" int cohcuda_host_xor_deferred(void)
 {
     static const int deferred = [] { const char *e = std::getenv("COHCUDA_HOST_XOR_ON_CALL"); return (e && std::atoi(e)) ? 0 : 1; }();
     return deferred;
 }
+namespace {
+// byte ranges whose in-place XOR was deferred (the librtlsdr ring: asyncbufn = 8 buffers per dongle, fixed
+// addresses for the life of the device, include/common.h:114-122) -- a few hundred entries at most
+std::mutex g_pending_mtx;
+std::vector<std::pair<const uint8_t *, size_t>> g_pending;
+bool pending_covers(const void *p, size_t n)
+{
+    const uint8_t *b = static_cast<const uint8_t *>(p);
+    std::lock_guard<std::mutex> lk(g_pending_mtx);
+    for (const auto &r : g_pending)
+        if (b >= r.first && b + n <= r.first + r.second) return true;
+    return false;
+}
+void pending_add(const uint8_t *p, size_t n)
+{
+    std::lock_guard<std::mutex> lk(g_pending_mtx);
+    for (auto &r : g_pending)
+        if (r.first == p) { if (n > r.second) r.second = n; return; }
+    g_pending.emplace_back(p, n);
+}
+// int8 -> float of a source that may still be offset-binary: the pending XOR runs as its own kernel first
+void convtofloat_any(float *out, const int8_t *s8bit, int n)
+{
+    if (n > 0 && cohcuda_host_xor_deferred() && pending_covers(s8bit, (size_t)n)) {
+        const int n8 = (n + 7) & ~7;                                  // the XOR kernel works on 8-byte words
+        std::vector<uint8_t> raw((size_t)n8, 0x80), sgn((size_t)n8);
+        std::copy(reinterpret_cast<const uint8_t *>(s8bit), reinterpret_cast<const uint8_t *>(s8bit) + n, raw.begin());
+        PRIM(cohcuda_cdsp_convtosigned(H, raw.data(), sgn.data(), n8));
+        PRIM(cohcuda_cdsp_convtofloat(H, out, reinterpret_cast<const int8_t *>(sgn.data()), n));
+        return;
+    }
+    PRIM(cohcuda_cdsp_convtofloat(H, out, s8bit, n));
+}
+}  // namespace
+
+extern "C" int cohcuda_host_xor_pending(const void *p, size_t n) { return pending_covers(p, n) ? 1 : 0; }
+extern "C" void cohcuda_host_xor_forget(const void *p)
+{
+    std::lock_guard<std::mutex> lk(g_pending_mtx);
+    for (size_t i = 0; i < g_pending.size(); i++)
+        if (g_pending[i].first == p) { g_pending.erase(g_pending.begin() + i); return; }
+}
+
 void cdsp::convtosigned(const uint8_t *in, const uint8_t *out, int n)
 {
-    if (in == out && cohcuda_host_xor_deferred()) return;
+    if (in == out && cohcuda_host_xor_deferred()) { if (n > 0) pending_add(in, (size_t)n); return; }
     PRIM(cohcuda_cdsp_convtosigned(H, in, const_cast<uint8_t *>(out), n));
 }
 
 // src/cdsp.cc:36-39
 const float *cdsp::convtofloat(const float *out, const int8_t *s8bit, int n)
 {
-    PRIM(cohcuda_cdsp_convtofloat(H, const_cast<float *>(out), s8bit, n));
+    convtofloat_any(const_cast<float *>(out), s8bit, n);
     return out;
 }
 
 // src/cdsp.cc:41-44 (n = number of int8 values = 2 x complex samples)
 const std::complex<float> *cdsp::convtofloat(const std::complex<float> *out, const int8_t *s8bit, int n)
 {
-    PRIM(cohcuda_cdsp_convtofloat(H, reinterpret_cast<float *>(const_cast<std::complex<float> *>(out)), s8bit, n));
+    convtofloat_any(reinterpret_cast<float *>(const_cast<std::complex<float> *>(out)), s8bit, n);
     return out;
 }
 

@@ -4,6 +4,7 @@
  * (include/cdsp.h, include/ccoherent.h), unchanged. */
 #ifndef COHCUDA_HOST_H
 #define COHCUDA_HOST_H
+#include <stddef.h>
 #include "coherent_cuda.h"
 #ifdef __cplusplus
 extern "C" {
@@ -18,6 +19,14 @@ void cohcuda_host_destroy_fft_scheme(void *scheme);
  * callback thread (include/common.h:121) -- is deferred to the kernels' load path; the DSP thread then
  * submits offset-binary buffers with input_is_signed = 0.  0 when COHCUDA_HOST_XOR_ON_CALL=1. */
 int cohcuda_host_xor_deferred(void);
+/* 1 if [p, p+n) lies inside a buffer whose in-place convtosigned was deferred, i.e. its bytes are still
+ * offset-binary.  cdsp::convtofloat consults the same record and applies the pending XOR itself, so code
+ * that reads such buffers through cdsp:: (console `phase`, src/console.cc:295-299) sees signed samples;
+ * only code that reads the raw bytes directly needs to ask. */
+int cohcuda_host_xor_pending(const void *p, size_t n);
+/* drops the record of the buffer that starts at p: call it when such a buffer is freed (the record is
+ * keyed by address and would otherwise outlive it; librtlsdr's ring lives as long as the device) */
+void cohcuda_host_xor_forget(const void *p);
 /* the engine a ccoherent instance drives (NULL if none is alive); for status displays/tests */
 cohcuda_t *cohcuda_host_engine(const void *ccoherent_instance);
 #ifdef __cplusplus

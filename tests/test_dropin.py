@@ -15,7 +15,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 _GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["four_cfg", "edge_delay", "mixed_slots", "raw_mode", "track_only"]
+CASES = ["four_cfg", "edge_delay", "mixed_slots", "raw_mode", "track_only", "ura21_nfft8", "ura21_nfft22"]
 
 
 @pytest.fixture(scope="module")
@@ -42,6 +42,41 @@ def test_dropin_tus_reproduce_reference_packets(oracle, dropin, name):
     np.testing.assert_array_equal(a[:, :B], b[:, :B])                   # reference column: raw signed bytes
     assert np.abs(a - b).max() <= 1                                     # isolated +-1 LSB (exact vs float dot)
     assert (a != b).mean() < 1e-3
+
+
+def test_inplace_convtosigned_keeps_its_contract_for_cdsp_readers(oracle, dropin):
+    """cbuffer::setbufferptr converts the USB buffer in place (include/common.h:121).  The drop-in defers
+    that XOR to the kernels, so the bytes stay offset-binary -- but whoever reads the buffer through cdsp::
+    (console `phase`: csdrdevice::convtofloat -> cdsp::convtofloat, src/console.cc:295-299) must still get
+    the signed samples the reference would have produced."""
+    import ctypes as Ct
+    D = oracle.ref_lib(dropin)
+    D.cohcuda_host_xor_pending.argtypes = [Ct.c_void_p, Ct.c_size_t]
+    rng = np.random.default_rng(9)
+    D.cohcuda_host_xor_forget.argtypes = [Ct.c_void_p]
+    p = lambda a: a.ctypes.data_as(Ct.c_void_p)
+    for n in (16384, 4096 + 8):
+        ring = rng.integers(0, 256, n, dtype=np.uint8)
+        raw = ring.copy()
+        want = (raw ^ 0x80).view(np.int8).astype(np.float32) * np.float32(1.0 / 127.0)
+        assert D.cohcuda_host_xor_pending(p(ring), n) == 0
+        D.refh_cdsp_convtosigned(p(ring), p(ring), n)                      # in place: deferred, recorded
+        assert D.cohcuda_host_xor_pending(p(ring), n) == 1
+        f = np.zeros(n, np.float32); D.refh_cdsp_convtofloat(p(f), p(ring), n)
+        np.testing.assert_array_equal(f, want)                            # bit-exact, as src/cdsp.cc:41-44 on signed bytes
+        half = np.zeros(n // 2 - 3, np.float32)                           # a sub-range (odd length) of the same buffer
+        D.refh_cdsp_convtofloat(p(half), Ct.c_void_p(ring.ctypes.data + 5), half.size)
+        np.testing.assert_array_equal(half, want[5:5 + half.size])
+        ring[:] = rng.integers(0, 256, n, dtype=np.uint8)                  # next USB transfer lands in the same buffer
+        D.refh_cdsp_convtosigned(p(ring), p(ring), n)
+        f2 = np.zeros(n, np.float32); D.refh_cdsp_convtofloat(p(f2), p(ring), n)
+        np.testing.assert_array_equal(f2, (ring ^ 0x80).view(np.int8).astype(np.float32) * np.float32(1.0 / 127.0))
+        # a buffer that was never converted in place is taken as signed, as before
+        other = rng.integers(0, 256, n, dtype=np.uint8)
+        f3 = np.zeros(n, np.float32); D.refh_cdsp_convtofloat(p(f3), p(other), n)
+        np.testing.assert_array_equal(f3, other.view(np.int8).astype(np.float32) * np.float32(1.0 / 127.0))
+        D.cohcuda_host_xor_forget(p(ring))                                # the buffer is released: its record goes with it
+        assert D.cohcuda_host_xor_pending(p(ring), n) == 0
 
 
 def test_dropin_cdsp_statics_match_reference(oracle, dropin):
