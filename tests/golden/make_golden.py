@@ -38,6 +38,14 @@ CASES = {
                         steps=[(5, 1, 11), (9, 3, -70), (12, 1, -2)], late={9: 3}),
     # a block longer than one SM's shared memory holds (L = 16384 > 8192: the split-transform path)
     "long_block": dict(C=2, B=32768, nb=3, noheader=0, delays=[100, -3000], req="all", noise="on"),
+    # round 3: the two geometries the benchmarks run.  URA21 (examplecfg/URA21.cfg:5-26: 21 + 1 dongles) with the stock
+    # nfft = 8 (seven channels served per block, src/ccoherent.cc:124) and with nfft = 22 (every channel, every block:
+    # the bench's SYNC mode); BASELINE config 3's 65536-sample blocks
+    "ura21_nfft8": dict(C=21, B=16384, nb=3, noheader=0, req="all", noise="on", nfft=8,
+                        delays=[0, 17, -250, 64, -64, 1, -1, 33, -47, 12, -12, 5, -5, 60, -60, 25, -25, 8, -8, 40, -40]),
+    "ura21_nfft22": dict(C=21, B=16384, nb=3, noheader=0, req="all", noise="on", nfft=22,
+                         delays=[0, 17, -250, 64, -64, 1, -1, 33, -47, 12, -12, 5, -5, 60, -60, 25, -25, 8, -8, 40, -40]),
+    "big65536": dict(C=2, B=131072, nb=2, noheader=0, delays=[1000, -20000], req="all", noise="on"),
 }
 
 
@@ -66,12 +74,13 @@ def build_case(name, spec):
     if spec["noise"] == "gated":
         noise[nb // 4: nb // 2] = 0
         noise[-3:] = 0
-    with O.RefCdsp(C, B, noheader=bool(spec["noheader"]), nfft=8) as R:
+    nfft = spec.get("nfft", 8)
+    with O.RefCdsp(C, B, noheader=bool(spec["noheader"]), nfft=nfft) as R:
         out = R.run_batch(iq, lag_request=req, refnoise=noise)
         sent_len = R.sent_len
     return dict(iq=iq, lag_request=req, refnoise=noise, packets=out["packets"], lag=out["lag"],
                 mag=out["mag"], phase=out["phase"], measured=out["measured"],
-                meta=np.array([C, B, nb, spec["noheader"], 8, sent_len], dtype=np.int64),
+                meta=np.array([C, B, nb, spec["noheader"], nfft, sent_len], dtype=np.int64),
                 delays=np.array(spec["delays"], dtype=np.int64), phases=info["phases"], delay_matrix=info["delays"])
 
 

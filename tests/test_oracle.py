@@ -23,7 +23,7 @@ def load_case(name):
 
 def test_golden_fixtures_present():
     assert {"four_cfg", "edge_delay", "mixed_slots", "raw_mode", "track_only", "dead_channel", "delay_steps",
-            "long_block"} <= set(CASES)
+            "long_block", "ura21_nfft8", "ura21_nfft22", "big65536"} <= set(CASES)
 
 
 @pytest.mark.parametrize("name", CASES)
