@@ -45,6 +45,12 @@ static const orc_plan *get_plan(int n)
  * A complex float is one 64-bit lane; a __m256 holds four of them {re0 im0 re1 im1 ...}.
  * round 2: the scalar passes left the s = 1 / 4 / 16 inner loops unvectorised (224 us per 16384-point
  * transform against 111 us for scipy's pocketfft); these run at pocketfft speed or better. */
+#ifndef __AVX2__
+/* There is deliberately no scalar variant: the committed goldens (the npz files under tests/golden) carry THIS code's
+ * rounding (FMA contraction inside the intrinsics), and a second code path with different rounding would
+ * be a second, unpinned checker.  oracle/Makefile builds with -march=x86-64-v3. */
+#error "cdsp_oracle_fft.c needs AVX2 + FMA (build with -march=x86-64-v3 as oracle/Makefile does)"
+#endif
 #include <immintrin.h>
 
 static inline __m256 cmul4(__m256 a, __m256 wr, __m256 wi)       /* a * (wr + j wi), lane-wise */
@@ -169,7 +175,12 @@ void orc_fft(orc_cf32 *out, const orc_cf32 *in, int n, int sign)
     const orc_cf32 *tw = pl->tw;
     /* per-thread scratch, grown on demand (no malloc per call) */
     static __thread orc_cf32 *tmp = NULL; static __thread int tmp_n = 0;
-    if (tmp_n < n) { free(tmp); tmp = (orc_cf32 *)aligned_alloc(64, sizeof(orc_cf32) * (size_t)n); tmp_n = n; }
+    if (tmp_n < n) {
+        /* aligned_alloc wants a size that is a multiple of the alignment (n < 8 would not be).  The buffer
+         * lives as long as its thread (a few worker threads of the harness; never per call). */
+        const size_t bytes = (sizeof(orc_cf32) * (size_t)n + 63) / 64 * 64;
+        free(tmp); tmp = (orc_cf32 *)aligned_alloc(64, bytes); tmp_n = n;
+    }
     int passes = 0;
     for (int nc = n; nc > 1; nc = (nc >= 4) ? nc >> 2 : nc >> 1) passes++;
     /* ping-pong so that the last pass lands in out; the first pass reads in (never written) */
