@@ -46,7 +46,8 @@ STATIC_MAX_BLOCKSIZE, STATIC_MAX_SPECTRUM_BYTES, STATIC_MAX_ITEMS = 16384, 4 << 
 class Config(C.Structure):
     _fields_ = [("n_signal", C.c_uint32), ("blocksize", C.c_uint32), ("max_lag_slots", C.c_uint32),
                 ("alpha", C.c_float), ("noheader", C.c_int), ("apply_shift", C.c_int),
-                ("device", C.c_int), ("max_batch_blocks", C.c_uint32), ("stream", C.c_void_p)]
+                ("device", C.c_int), ("max_batch_blocks", C.c_uint32), ("stream", C.c_void_p),
+                ("pipe_chunk_blocks", C.c_uint32)]
 
 
 class ChanState(C.Structure):
@@ -74,7 +75,7 @@ class BatchArgs(C.Structure):
 class GatherConfig(C.Structure):
     _fields_ = [("rank", C.c_int), ("n_ranks", C.c_int), ("root", C.c_int), ("shard", C.c_int),
                 ("transport", C.c_int), ("rank_count", C.POINTER(C.c_uint32)), ("max_blocks", C.c_uint32),
-                ("chunk_blocks", C.c_uint32), ("store_ctas", C.c_uint32)]
+                ("chunk_blocks", C.c_uint32), ("store_ctas", C.c_uint32), ("reserve_sms", C.c_int32)]
 
 
 class GatherGeometry(C.Structure):
@@ -189,10 +190,10 @@ class CoherentCuda:
     the DSP members of csdrdevice + cpacketize::write in the reference)."""
 
     def __init__(self, n_signal, blocksize, alpha=0.5, noheader=False, apply_shift=False,
-                 max_lag_slots=0, device=0, max_batch_blocks=1, stream=None):
+                 max_lag_slots=0, device=0, max_batch_blocks=1, stream=None, pipe_chunk_blocks=0):
         self.lib = load_library()
         self.cfg = Config(n_signal, blocksize, max_lag_slots, alpha, int(noheader), int(apply_shift),
-                          device, max_batch_blocks, stream)
+                          device, max_batch_blocks, stream, pipe_chunk_blocks)
         self.h = C.c_void_p()
         rc = self.lib.cohcuda_create(C.byref(self.cfg), C.byref(self.h))
         if rc != 0:
@@ -266,9 +267,9 @@ class CoherentCuda:
 
     # ---- multi-GPU gather (one handle per rank; the blob travels through the caller's plumbing) -----
     def gather_init(self, rank, n_ranks, rank_count, shard, transport=GATHER_NCCL, max_blocks=1, root=0,
-                    chunk_blocks=0, store_ctas=0):
+                    chunk_blocks=0, store_ctas=0, reserve_sms=0):
         cnt = (C.c_uint32 * n_ranks)(*[int(v) for v in rank_count])
-        cfg = GatherConfig(rank, n_ranks, root, shard, transport, cnt, max_blocks, chunk_blocks, store_ctas)
+        cfg = GatherConfig(rank, n_ranks, root, shard, transport, cnt, max_blocks, chunk_blocks, store_ctas, reserve_sms)
         self._check(self.lib.cohcuda_gather_init(self.h, C.byref(cfg)), "cohcuda_gather_init")
         g = GatherGeometry()
         self._check(self.lib.cohcuda_gather_geometry_of(self.h, C.byref(g)), "cohcuda_gather_geometry_of")

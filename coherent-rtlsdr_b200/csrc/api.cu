@@ -107,18 +107,13 @@ extern "C" int cohcuda_create(const cohcuda_config *cfg, cohcuda_t **out) {
         if ((e = cudaMemcpy(h->d_TN, tn.data(), sizeof(float2) * h->L, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy", e);
     }
     h->corr_chunk = kCorrChunk;
-    if (const char *e = getenv("COHCUDA_CORR_CHUNK")) {              // tuning knob: blocks per K1/K2 launch
-        if (atoi(e) >= 1 && atoi(e) <= 4096) h->corr_chunk = (uint32_t)atoi(e);
-    }
-    if (const char *e = getenv("COHCUDA_PIPE_CHUNK")) {              // tuning knob: blocks per pipeline stage of host-buffer batches
-        if (atoi(e) >= 1 && atoi(e) <= (int)kCorrChunk) h->pipe_chunk_env = (uint32_t)atoi(e);
-    }
+    if (cfg->pipe_chunk_blocks > kCorrChunk) { g_create_error = "pipe_chunk_blocks must be at most 1024"; cohcuda_destroy(h); return COHCUDA_ERR_ARG; }
+    h->pipe_chunk_cfg = cfg->pipe_chunk_blocks;
     if (correlate_supported(B) && correlate_is_big(B)) {
         // the split path keeps 16 L bytes of scratch per item in flight: bound the items per launch group
-        uint32_t big_items = 2048;                     // swept 256..5376 at L = 65536: 45.6 -> 52.2 G samples/s (2 GiB of scratch)
-        if (const char *e = getenv("COHCUDA_BIG_ITEMS")) { if (atoi(e) >= 1 && atoi(e) <= 65536) big_items = (uint32_t)atoi(e); }
-        uint32_t cc = big_items / cfg->n_signal;
-        h->corr_chunk = cc < 1 ? 1 : (cc > kCorrChunk ? kCorrChunk : cc);
+        const uint32_t big_items = 2048;               // swept 256..5376 at L = 65536: 45.6 -> 52.2 G samples/s (2 GiB of scratch)
+        h->big_items = big_items;
+        h->corr_chunk = big_corr_chunk(big_items, cfg->n_signal);
         std::vector<float2> ts(8192);
         for (uint32_t n = 0; n < 8192; n++) {
             double a = -2.0 * M_PI * (double)n / 16384.0;

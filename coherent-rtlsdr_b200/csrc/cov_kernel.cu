@@ -178,8 +178,7 @@ k_covariance_mma(const int8_t *__restrict__ packets, size_t pitch, size_t lead, 
 cudaError_t launch_covariance(const int8_t *packets, size_t pitch, size_t lead, size_t hdr, uint32_t nch, uint32_t B,
                               uint32_t n_blocks, long long *S, int *m, cudaStream_t st) {
     if (n_blocks == 0) return cudaSuccess;
-    const char *force = getenv("COHCUDA_COV_DP4A");
-    if (nch <= 22 && B >= 64 && !(force && atoi(force))) {
+    if (nch <= 22 && B >= 64) {
         // every element is written by the kernel (i <= j and m); zero the rest for the host's symmetry fill
         cudaError_t e0 = cudaMemsetAsync(S, 0, (size_t)n_blocks * nch * nch * 2 * sizeof(long long), st);
         if (e0 != cudaSuccess) return e0;

@@ -26,7 +26,8 @@ struct cohcuda {
     float2 *d_TN = nullptr, *d_TN_sub = nullptr;   // W_N^n (n < L) and, for L > 8192, W_16384^n (n < 8192)
     float4 *d_scratch = nullptr;                   // L > 8192: [corr_chunk * C][L] packed elements (fft_big.cu)
     uint32_t corr_chunk = 0;                       // blocks per K1/K2 launch group
-    uint32_t pipe_chunk_env = 0;                   // COHCUDA_PIPE_CHUNK tuning knob, read once at create
+    uint32_t big_items = 0;                        // L > 8192: items per launch group the scratch holds (0 on the small path)
+    uint32_t pipe_chunk_cfg = 0;                   // cohcuda_config.pipe_chunk_blocks (0 = default)
     size_t readcnt_cap = 0;                        // words d_readcnt holds
     ChanState *d_state[2] = { nullptr, nullptr };
     int cur = 0;
@@ -67,6 +68,14 @@ static constexpr uint32_t kCorrChunk = 1024;            // blocks per K1/K2 laun
                                                         // measured 148 -> 1024: +3 % (fewer launch tails), the spectra then live in HBM not L2
 static constexpr uint32_t kPipeChunk = 148;             // same, when host copies are pipelined around the kernels (swept 24..512 with
                                                         // batches overlapping: 148 best, 7.99 ms per 1024-block URA21 step)
+
+// blocks per launch group of the large-block path (fft_big.cu) for an engine of n_signal channels: the scratch
+// holds big_items items.  A function of n_signal only, so that every rank of a channel-sharded gather can work
+// out every other rank's value (api_gather.inc)
+static inline uint32_t big_corr_chunk(uint32_t big_items, uint32_t n_signal) {
+    const uint32_t cc = big_items / (n_signal ? n_signal : 1);
+    return cc < 1 ? 1 : (cc > kCorrChunk ? kCorrChunk : cc);
+}
 
 #define CK(call)                                                                        \
     do {                                                                                \

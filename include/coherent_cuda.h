@@ -52,6 +52,10 @@ typedef struct {
     int      device;            /* CUDA device ordinal                                        */
     uint32_t max_batch_blocks;  /* capacity hint for cohcuda_batch (grows on demand)          */
     void    *stream;            /* cudaStream_t to enqueue on, or NULL for a private stream   */
+    uint32_t pipe_chunk_blocks; /* tuning: blocks per pipeline stage of host-buffer batches (H2D copy of
+                                   stage k+1 | kernels of stage k | read-back of stage k-1); 0 = default
+                                   (148 blocks of 22 x 16 KiB, scaled by bytes for other shapes), max 1024.
+                                   Results do not depend on it.  The library reads no environment variables. */
 } cohcuda_config;
 
 /* per-channel state that survives across blocks (include/csdrdevice.h:74-89) */
@@ -272,6 +276,8 @@ typedef struct {
     uint32_t max_blocks;          /* blocks per gathered batch the buffers must hold            */
     uint32_t chunk_blocks;        /* blocks per transfer, 0 = default                           */
     uint32_t store_ctas;          /* PEER_STORE: CTAs of the storing k_apply, 0 = default       */
+    int32_t  reserve_sms;         /* NCCL: SMs the persistent kernels leave free for NCCL's send / receive
+                                     kernels; 0 = default (16), negative = none, at most half the GPU    */
 } cohcuda_gather_config;
 
 typedef struct {

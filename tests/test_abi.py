@@ -40,8 +40,10 @@ def test_struct_layouts_match_header(pkg, tmp_path):
 #include <stddef.h>
 #include "coherent_cuda.h"
 int main(void) {
-    printf("%zu %zu %zu %zu\n", sizeof(cohcuda_config), sizeof(cohcuda_chan_state), sizeof(cohcuda_result), sizeof(cohcuda_batch_args));
-    printf("%zu %zu %zu\n", offsetof(cohcuda_config, stream), offsetof(cohcuda_batch_args, cf32), offsetof(cohcuda_result, globalseqn));
+    printf("%zu %zu %zu %zu %zu %zu\n", sizeof(cohcuda_config), sizeof(cohcuda_chan_state), sizeof(cohcuda_result), sizeof(cohcuda_batch_args),
+           sizeof(cohcuda_gather_config), sizeof(cohcuda_gather_geometry));
+    printf("%zu %zu %zu %zu %zu\n", offsetof(cohcuda_config, stream), offsetof(cohcuda_batch_args, cf32), offsetof(cohcuda_result, globalseqn),
+           offsetof(cohcuda_config, pipe_chunk_blocks), offsetof(cohcuda_gather_config, reserve_sms));
     return 0;
 }''')
     exe = tmp_path / "lay"
@@ -49,8 +51,10 @@ int main(void) {
     a, b = subprocess.check_output([str(exe)], text=True).strip().split("\n")
     sizes = [int(x) for x in a.split()]
     offs = [int(x) for x in b.split()]
-    assert sizes == [C.sizeof(pkg.Config), C.sizeof(pkg.ChanState), C.sizeof(pkg.Result), C.sizeof(pkg.BatchArgs)]
-    assert offs == [pkg.Config.stream.offset, pkg.BatchArgs.cf32.offset, pkg.Result.globalseqn.offset]
+    assert sizes == [C.sizeof(pkg.Config), C.sizeof(pkg.ChanState), C.sizeof(pkg.Result), C.sizeof(pkg.BatchArgs),
+                     C.sizeof(pkg.GatherConfig), C.sizeof(pkg.GatherGeometry)]
+    assert offs == [pkg.Config.stream.offset, pkg.BatchArgs.cf32.offset, pkg.Result.globalseqn.offset,
+                    pkg.Config.pipe_chunk_blocks.offset, pkg.GatherConfig.reserve_sms.offset]
 
 
 def test_no_cpu_fallback(pkg):

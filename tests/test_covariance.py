@@ -27,12 +27,11 @@ def test_rxx_from_sums_is_the_client_formula(pkg):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("C,B,nb", [(21, 16384, 12), (3, 4096, 5), (40, 1024, 3), (2, 131072, 2)])
-@pytest.mark.parametrize("path", ["mma", "dp4a"])
-def test_covariance_sums_exact(pkg, synth, monkeypatch, C, B, nb, path):
-    """Both kernels of cov_kernel.cu: int8 tensor-core MMA (up to 22 columns) and the dp4a fallback."""
-    if path == "dp4a":
-        monkeypatch.setenv("COHCUDA_COV_DP4A", "1")
+@pytest.mark.parametrize("C,B,nb", [(21, 16384, 12), (3, 4096, 5), (2, 131072, 2),
+                                    (40, 1024, 3), (30, 16384, 4), (22, 4096, 3)])
+def test_covariance_sums_exact(pkg, synth, C, B, nb):
+    """Both kernels of cov_kernel.cu: int8 tensor-core MMA (up to 22 columns, the first three cases) and the
+    dp4a kernel that takes over above that (the last three)."""
     L = B // 2
     iq, _ = synth.make_blocks(C, B, nb, seed=77 + C, delays=np.zeros(C, dtype=int))
     # full-scale bytes on one channel: the extremes (-128) must not wrap anywhere in the integer path

@@ -36,7 +36,9 @@ def _check(pkg, oracle, got, iq, req, noise, C, B, slots, shift=1):
 @pytest.mark.parametrize("mode,C,B,nb,slots,transport", [
     ("channels", 21, 16384, 40, 7, "nccl"), ("channels", 21, 16384, 40, 7, "peer_copy"), ("channels", 21, 16384, 40, 7, "peer_store"),
     ("blocks", 21, 16384, 140, 0, "nccl"), ("blocks", 5, 512, 230, 0, "peer_copy"), ("blocks", 5, 512, 230, 0, "peer_store"),
-    ("channels", 6, 2048, 64, 0, "nccl")])
+    ("channels", 6, 2048, 64, 0, "nccl"),
+    # the large-block path (fft_big.cu) under a gather, uneven channel groups (5 = 3 + 2 on two GPUs)
+    ("channels", 5, 32768, 20, 0, "nccl"), ("channels", 5, 32768, 20, 0, "peer_copy"), ("blocks", 3, 65536, 24, 0, "peer_store")])
 def test_gathered_matrix_equals_single_gpu(pkg, synth, oracle, tmp_path, mode, C, B, nb, slots, transport):
     world = min(_ngpu(), 8, C if mode == "channels" else 8)
     if world < 2:

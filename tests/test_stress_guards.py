@@ -52,8 +52,7 @@ def test_repeated_runs_are_bit_identical_under_contention(pkg, synth, oracle, mo
     filler = torch.empty(64 << 20, dtype=torch.float32, device="cuda")
     side = torch.cuda.Stream()
     for rep in range(12):
-        monkeypatch.setenv("COHCUDA_PIPE_CHUNK", str([0, 7, 33, 148][rep % 4]) if rep % 4 else "148")
-        eng = pkg.CoherentCuda(C, B, apply_shift=True)
+        eng = pkg.CoherentCuda(C, B, apply_shift=True, pipe_chunk_blocks=[148, 7, 33, 0][rep % 4])   # pipeline stage size must not matter
         with torch.cuda.stream(side):                       # unrelated traffic competing for SMs, L2 and HBM
             for _ in range(4):
                 filler.mul_(1.0001)
@@ -107,4 +106,33 @@ def test_gather_api_on_a_single_rank(pkg, synth, oracle, transport, shard):
         eng2.close()
     with pytest.raises(pkg.CohCudaError):
         eng.batch(iq[:5], lag_mode=pkg.LAG_ALL, gather=True, gather_skip_blocks=9)       # halo longer than the call
+    with pytest.raises(pkg.CohCudaError, match="already attached"):
+        eng.gather_attach(eng.gather_export())                                          # one attach per gather_init
     eng.close()
+
+
+def test_gather_chunk_is_the_same_on_every_rank(pkg):
+    """The transfer chunk must not depend on the rank: on the large-block path a rank's launch group shrinks
+    with its channel count (2048 / n_signal blocks), and channel shards may be uneven (21 + 20 channels at
+    B = 32768: 97 vs 102 blocks).  Sender and receiver would then walk different chunk lists -- an NCCL hang or
+    misplaced columns.  Every rank now arrives at the minimum over all ranks, and the root's value travels in
+    the blob so that gather_attach refuses a mismatch instead.  (Single GPU: each engine plays the root once.)"""
+    import struct
+    B, counts, chunks = 32768, [21, 20], []
+    for rank in (0, 1):
+        eng = pkg.CoherentCuda(counts[rank], B)
+        eng.gather_init(rank, 2, counts, pkg.SHARD_CHANNELS, pkg.GATHER_PEER_COPY, max_blocks=2, root=rank)
+        blob = eng.gather_export()
+        magic, transport, chunk = struct.unpack_from("<III", blob)
+        chunks.append(chunk)
+        bad = blob[:8] + struct.pack("<I", chunk + 5) + blob[12:]
+        with pytest.raises(pkg.CohCudaError, match="transfer chunk differs"):
+            eng.gather_attach(bad)
+        eng.close()
+    assert chunks == [2048 // 21, 2048 // 21]
+    # an explicit chunk below every rank's launch group is taken as given, on every rank
+    for rank in (0, 1):
+        eng = pkg.CoherentCuda(counts[rank], B)
+        eng.gather_init(rank, 2, counts, pkg.SHARD_CHANNELS, pkg.GATHER_PEER_COPY, max_blocks=2, root=rank, chunk_blocks=16)
+        assert struct.unpack_from("<III", eng.gather_export())[2] == 16
+        eng.close()
