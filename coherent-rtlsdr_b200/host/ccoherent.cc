@@ -28,6 +28,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -50,7 +51,13 @@ struct Engine {
     // changes (a dongle starts or stops, console add / del) the engine's per-channel state no longer
     // belongs to the device in that slot and is re-seeded from the devices' own phasecorr / phasecorrprev
     std::vector<std::pair<const void *, uint8_t>> slots;
+    // error bookkeeping of the per-block path (see drop_block below)
+    uint64_t dropped = 0;                       // blocks consumed without a packet because the library call failed
+    uint32_t consecutive = 0;                   // ... in a row; kRebuildAfter of them rebuild the engine once
+    bool rebuilt = false, pin_warned = false;
 };
+constexpr uint32_t kRebuildAfter = 50;
+std::atomic<int> g_inject_failures{0};          // test hook: the next n submits are treated as failed
 
 std::map<const ccoherent *, Engine *> g_engines;
 std::mutex g_engines_mtx;
@@ -111,7 +118,41 @@ void pin_once(Engine *e, const void *p, size_t bytes)
 {
     for (const void *q : e->pinned) if (q == p) return;
     e->pinned.push_back(p);
-    (void)cohcuda_register_host(e->h, const_cast<void *>(p), bytes);
+    if (cohcuda_register_host(e->h, const_cast<void *>(p), bytes) != COHCUDA_OK && !e->pin_warned) {
+        e->pin_warned = true;                   // said once: the path still works, only slower
+        std::fprintf(stderr, "ccoherent (libcoherent_cuda): a USB buffer could not be pinned (%s); its copies are staged by the driver\n",
+                     cohcuda_last_error(e->h));
+    }
+}
+
+// A failed library call on the per-block path must not take a receiver down that has been running for days
+// next to hot-plugged USB hardware.  The block is dropped: every device's buffer is consumed, nothing is
+// written or sent, and the clients see the gap in readcnt / globalseqn exactly as they do when the reference
+// loses USB transfers (src/cpacketizer.cc:137-156, 113).  kRebuildAfter failures in a row rebuild the engine
+// once (a sticky CUDA error does not heal by itself); if that does not help either there is no path left --
+// no CPU fallback exists by design -- and the process stops with the library's message.
+void drop_block(ccoherent *ctx, Engine *e, const char *what)
+{
+    e->dropped++; e->consecutive++;
+    if (e->consecutive == 1 || e->consecutive % 1000 == 0)
+        std::fprintf(stderr, "ccoherent (libcoherent_cuda): %s: %s -- block dropped (%llu so far)\n", what,
+                     e->h ? cohcuda_last_error(e->h) : "no engine", (unsigned long long)e->dropped);
+    ctx->refdev->consume();
+    uint32_t k = 1;
+    for (auto *d : *ctx->devices) { if (k < e->ready.size() && e->ready[k]) d->consume(); k++; }
+    if (e->consecutive >= kRebuildAfter) {
+        if (e->rebuilt) die(what, e->h);
+        std::fprintf(stderr, "ccoherent (libcoherent_cuda): %u failures in a row, rebuilding the engine\n", e->consecutive);
+        std::vector<cohcuda_chan_state> keep(e->n_signal + 1);
+        const bool have = e->h && cohcuda_get_state(e->h, keep.data(), e->n_signal + 1) == COHCUDA_OK;
+        if (e->h) cohcuda_destroy(e->h);
+        e->h = nullptr; e->pinned.clear(); e->slots.clear();
+        const uint32_t n = e->n_signal, B = e->B;
+        e->n_signal = 0;
+        size_engine(e, n, B);                   // dies if the device is gone for good
+        if (have) (void)cohcuda_set_state(e->h, keep.data(), n + 1);
+        e->rebuilt = true; e->consecutive = 0;
+    }
 }
 
 }  // namespace
@@ -121,6 +162,15 @@ extern "C" cohcuda_t *cohcuda_host_engine(const void *inst)
     Engine *e = engine_of((const ccoherent *)inst);
     return e ? e->h : nullptr;
 }
+extern "C" uint64_t cohcuda_host_dropped_blocks(const void *inst)
+{
+    std::lock_guard<std::mutex> lock(g_engines_mtx);
+    if (inst) { auto it = g_engines.find((const ccoherent *)inst); return it == g_engines.end() ? 0 : it->second->dropped; }
+    uint64_t n = 0;
+    for (auto &kv : g_engines) n += kv.second->dropped;
+    return n;
+}
+extern "C" void cohcuda_host_inject_failures(int n) { g_inject_failures.store(n > 0 ? n : 0); }
 
 // src/ccoherent.cc:32-95 -- buffers and FFT plans become one library handle
 ccoherent::ccoherent(crefsdr *refdev_, lvector<csdrdevice *> *devvec_, crefnoise *refnoise_, int nfft_)
@@ -251,11 +301,16 @@ void ccoherent::threadf(ccoherent *ctx)
         // cbuffer::setbufferptr's in-place XOR (include/common.h:121) is deferred to the kernels' load path
         // (host/cdsp.cc): the buffers are still offset-binary unless COHCUDA_HOST_XOR_ON_CALL=1
         const int deferred = cohcuda_host_xor_deferred();
-        if (cohcuda_submit_block(e->h, e->chan.data(), e->readcnt.data(), e->request.data(),
-                                 ctx->refnoise->isenabled() ? 1 : 0, /*input_is_signed=*/deferred ? 0 : 1) != COHCUDA_OK)
-            die("cohcuda_submit_block", e->h);
-        if (cohcuda_wait_block(e->h, &e->res) != COHCUDA_OK) die("cohcuda_wait_block", e->h);
-        e->have_result = true;
+        int injected = g_inject_failures.load();
+        while (injected > 0 && !g_inject_failures.compare_exchange_weak(injected, injected - 1)) {}
+        if (injected > 0 ||
+            cohcuda_submit_block(e->h, e->chan.data(), e->readcnt.data(), e->request.data(),
+                                 ctx->refnoise->isenabled() ? 1 : 0, /*input_is_signed=*/deferred ? 0 : 1) != COHCUDA_OK) {
+            drop_block(ctx, e, injected > 0 ? "injected failure (test hook)" : "cohcuda_submit_block");
+            continue;                                                      // lag requests stay pending (csdrdevice.h:129-151)
+        }
+        if (cohcuda_wait_block(e->h, &e->res) != COHCUDA_OK) { drop_block(ctx, e, "cohcuda_wait_block"); continue; }
+        e->have_result = true; e->consecutive = 0; e->rebuilt = false;
 
         // reference column: raw signed bytes (:254-255) -- the library's column 0 when the XOR was deferred
         ctx->refdev->packetize.write(0, e->readcnt[0], deferred ? const_cast<int8_t *>(e->res.packet) : refsptr);

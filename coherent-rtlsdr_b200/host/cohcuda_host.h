@@ -5,6 +5,7 @@
 #ifndef COHCUDA_HOST_H
 #define COHCUDA_HOST_H
 #include <stddef.h>
+#include <stdint.h>
 #include "coherent_cuda.h"
 #ifdef __cplusplus
 extern "C" {
@@ -29,6 +30,13 @@ int cohcuda_host_xor_pending(const void *p, size_t n);
 void cohcuda_host_xor_forget(const void *p);
 /* the engine a ccoherent instance drives (NULL if none is alive); for status displays/tests */
 cohcuda_t *cohcuda_host_engine(const void *ccoherent_instance);
+/* blocks the DSP thread consumed WITHOUT publishing a packet because a library call failed (the clients
+ * see the gap in readcnt / globalseqn); instance NULL = all instances.  A failed call no longer aborts
+ * the process: the block is dropped, 50 failures in a row rebuild the engine once, and only if that
+ * fails too does the thread give up (there is no CPU path to fall back to). */
+uint64_t cohcuda_host_dropped_blocks(const void *ccoherent_instance);
+/* test hook: the next n blocks are treated as if cohcuda_submit_block had failed */
+void cohcuda_host_inject_failures(int n);
 #ifdef __cplusplus
 }
 #endif

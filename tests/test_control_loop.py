@@ -91,3 +91,39 @@ def test_dropin_gpu_path_closes_the_reference_control_loop(oracle):
     if not oracle.dropin_available():
         pytest.fail("oracle/_ref/libdropin_cuda.so is missing: run __graft_entry__.build() where /root/reference exists")
     _check(*_acquire(oracle, oracle.DROPIN_LIB_PATH))
+
+
+@pytest.mark.gpu
+def test_dropin_survives_failed_library_calls(oracle):
+    """A failed cohcuda_submit_block / wait_block must not abort a receiver that runs for days: the drop-in DSP
+    thread drops the block (consumes every ring, publishes nothing -- the clients see the gap in readcnt, as with
+    lost USB transfers, src/cpacketizer.cc:137-156), counts it and carries on; pending lag requests stay pending."""
+    import ctypes as Ct
+    if not oracle.dropin_available():
+        pytest.fail("oracle/_ref/libdropin_cuda.so is missing: run __graft_entry__.build() where /root/reference exists")
+    D = oracle.ref_lib(oracle.DROPIN_LIB_PATH)
+    D.cohcuda_host_dropped_blocks.restype = Ct.c_uint64
+    D.cohcuda_host_dropped_blocks.argtypes = [Ct.c_void_p]
+    D.cohcuda_host_inject_failures.argtypes = [Ct.c_int]
+    with oracle.RefLive(DELAYS, blocksize=16384, fs=1024000, nfft=8, gains=GAINS, phases=PHASES,
+                        lib_path=oracle.DROPIN_LIB_PATH) as lv:
+        t0 = time.time()
+        while time.time() - t0 < 40.0:
+            time.sleep(0.05)
+            st = lv.poll()
+            if st["synced"].all():
+                break
+        assert st["synced"].all()
+        before = int(D.cohcuda_host_dropped_blocks(None))
+        sent0 = lv.poll()["packets"]
+        D.cohcuda_host_inject_failures(7)
+        t0 = time.time()
+        while time.time() - t0 < 10.0 and int(D.cohcuda_host_dropped_blocks(None)) < before + 7:
+            time.sleep(0.02)
+        assert int(D.cohcuda_host_dropped_blocks(None)) == before + 7
+        time.sleep(0.5)                                          # 60 more blocks at 8 ms
+        st = lv.poll()
+        assert st["packets"] > sent0 + 20                        # the stream kept flowing after the gap
+        assert st["synced"].all() and (st["lag"][1:] == 0).all()
+        pkt = lv.last_packet()
+        assert pkt[:16].view(np.uint32)[1] == len(DELAYS) + 1    # and still publishes well-formed packets
