@@ -253,9 +253,20 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
             warp_argmax(best, bidx);
             if (lane == 0) { s_val[warp] = best; s_idx[warp] = bidx; }
         }
+#ifdef COH_EARLY_BEFORE_BAR
+        float4 r_early[kEarly ? kEarly : 1];
+#endif
         if (cur.valid) {
             mbar_wait(smem_u32(&s_bar[buf]), (i >> 1) & 1u);
             pass1_butterfly<LOG2L, false, 5>(raw0 + (size_t)buf * B, xormask, smem4, threadIdx.x, w_l, w_n);
+#ifdef COH_EARLY_BEFORE_BAR
+            // the first spectrum rows do not depend on shared memory: requested before the block barrier, their L2
+            // latency would overlap the wait for the slowest warp.  MEASURED SLOWER (round 3, B200): 1.719 -> 1.897 ms
+            // per 21 504 items (1.936 with COH_R_EARLY=4) -- eight float4 live across the barrier push the kernel
+            // deeper into its 128-register cap (spill loads 56 -> 96 B) and the rows of the fast warps arrive
+            // long before they are used.  Kept as a build variant only (profiles/r3_correlate_history.md).
+            fused_b_early<LOG2L>(refspec + (size_t)cur.slot * L, r_early);
+#endif
         }
         __syncthreads();
         if (prev.valid && warp == 0) {
@@ -266,8 +277,10 @@ k_correlate_persist(const uint8_t *__restrict__ iq, uint32_t nch, uint32_t B, co
         }
         if (!cur.valid) break;
         // ---- M(i) -------------------------------------------------------------------------------
+#ifndef COH_EARLY_BEFORE_BAR
         float4 r_early[kEarly ? kEarly : 1];
         fused_b_early<LOG2L>(refspec + (size_t)cur.slot * L, r_early);
+#endif
         mid_pass<LOG2L, P::RA, P::SA, -1, 5>(smem4, w_a);          // radix 16 at stride 32
         __syncwarp();
         fused_b_stage<LOG2L>(smem4, refspec + (size_t)cur.slot * L, r_early);   // 32-point stage, x conj(R), inverse 16-point DFT
